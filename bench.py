@@ -1,0 +1,476 @@
+#!/usr/bin/env python3
+"""bench.py -- train samples/s of the train.py step hot path on N B200s (one process per
+GPU), beside the reference's CPU path on the same box.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload wide4096|wide8192|tiny]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference ...      # the reference's CPU implementation, same metric/config
+
+One "step" = train.py:104-117 for one per-rank batch: on-device Philox batch generation
++ label rule, forward, BCE loss, backward, gradient all-reduce (N > 1), Adam.
+Default workload = BASELINE.json configs[3] (widened model: F=20, H=4096, 65536
+samples/GPU), the largest single-GPU configuration and the one the metric's roofline
+fraction is defined on (the B=4 reference shape is launch-latency-bound, its
+numbers ride along under "tiny").  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "distributed-gpu-test_b200"))
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    "wide4096": dict(B=65536, F=20, H=4096),
+    "wide8192": dict(B=65536, F=20, H=8192),
+    "tiny": dict(B=4, F=20, H=64),
+}
+SEED = 42
+LR = 1e-3
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="wide4096", choices=sorted(WORKLOADS))
+    ap.add_argument("--precision", default="auto", choices=["auto", "fp32", "bf16"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-tiny", action="store_true")
+    return ap.parse_known_args()[0]
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sus=d.get("bf16_tflops_sustained", d["bf16_tflops"]), src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sus=1400.0, src="fallback")   # B200_PROFILING.md fallback
+
+
+def init_flat(F, H):
+    """Initial weights in the reference's creation order (train.py:54,76): seed, then the two
+    nn.Linear default inits; flat layout [W1|b1|W2|b2]."""
+    torch.manual_seed(SEED)
+    l1, l2 = torch.nn.Linear(F, H), torch.nn.Linear(H, 1)
+    return torch.cat([t.detach().reshape(-1) for t in (l1.weight, l1.bias, l2.weight, l2.bias)])
+
+
+def label_rule(x):
+    f = x.shape[1]
+    return (x[:, : f // 2].sum(dim=1) > 0).float()
+
+
+def step_flops(B, F, H):
+    return B * (4 * F * H + 6 * H)           # algorithmic FLOPs per sample = 4FH + 6H
+
+
+# ------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """Samples SM clock / throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception as e:      # noqa: BLE001
+            self.nv = None
+            self.err = repr(e)
+
+    def sample(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        try:
+            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+            fn = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            bits = fn(self.h)
+            names = {
+                "hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4),
+            }
+            for k, b in names.items():
+                if bits & b:
+                    self.reasons.add(k)
+        except Exception:           # noqa: BLE001
+            pass
+
+    def start(self):
+        def run():
+            while not self._stop.wait(0.02):
+                self.sample()
+        self._thr = threading.Thread(target=run, daemon=True)
+        self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr:
+            self._thr.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------ reference arm (CPU)
+def cpu_reference_run(wl, steps, warmup, budget_s=None):
+    """The reference's own CPU path for this step (torch nn.Sequential + BCEWithLogitsLoss
+    + autograd + optim.Adam, as train.py:26-36,85,96,107-114 use them; DeepSpeed stage 0 at
+    world 1 adds nothing) via the oracle's torch-native restatement, on all host cores.
+    Each step works on a bounded sample of the per-GPU batch."""
+    from oracle import reference_step as ora
+    cores = len(os.sched_getaffinity(0))
+    torch.set_num_threads(cores)
+    B, F, H = wl["B"], wl["F"], wl["H"]
+    Bs = min(B, 8192)
+    torch.manual_seed(SEED)
+    p = ora.init_params(F, H)
+    state = {}
+
+    def one():
+        x = torch.randn(Bs, F)
+        y = ora.label_rule(x)
+        loss, _ = ora.torch_native_step(p, x, y, state, LR)
+        return float(loss)
+
+    for _ in range(max(1, warmup)):
+        one()
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(steps):
+        one()
+        done += 1
+        if budget_s is not None and time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return dict(value=Bs * done / dt, unit="samples/s", cores=cores, kind="port",
+                sample=f"{done} steps x {Bs} of the {B}-sample batch (F={F}, H={H}), torch {torch.__version__} CPU fp32, "
+                       f"{cores} threads, batch drawn with torch.randn on the host each step",
+                ms_per_step=1e3 * dt / done, steps=done, Bs=Bs)
+
+
+# ------------------------------------------------------------------------------ our arm
+class WideStep:
+    """Device-resident step for the widened workloads, every stage a libb200ds.so kernel."""
+
+    def __init__(self, lib, ctx, dev, wl, world, rank, precision):
+        from b200ds import _lib
+        self.lib, self.ctx, self._lib = lib, ctx, _lib
+        B, F, H = wl["B"], wl["F"], wl["H"]
+        self.B, self.F, self.H, self.world = B, F, H, world
+        self.P = F * H + 2 * H + 1
+        self.Ppad = (self.P + 3) // 4 * 4
+        self.precision = precision
+        flat = init_flat(F, H)
+        z = lambda n: torch.zeros(n, dtype=torch.float32, device=dev)      # noqa: E731
+        self.params = z(self.Ppad); self.params[: self.P] = flat.to(dev)
+        self.grads, self.m, self.v = z(self.Ppad), z(self.Ppad), z(self.Ppad)
+        self.x, self.y = z(B * F), z(B)
+        self.logits, self.dz, self.loss = z(B), z(B), z(1)
+        self.bce_sc = torch.zeros(lib.b200ds_bce_scratch_bytes(B), dtype=torch.uint8, device=dev)
+        self.bwd_sc = torch.zeros(max(256, lib.b200ds_mlp_backward_f32_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
+        self.counter = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.seed = SEED + 1000003 * rank           # distinct Philox key per rank
+        self.offset = 0
+        self.launches_per_step = 7
+        self.ev = None
+
+    def step(self, st, ev_pair=None):
+        lib, chk = self.lib, self._lib.check
+        B, F, H = self.B, self.F, self.H
+        adv = C.c_uint64(0)
+        chk(lib.b200ds_philox_normal(self.x.data_ptr(), B * F, self.seed, self.offset, C.byref(adv), st))
+        self.offset += adv.value
+        chk(lib.b200ds_label_rule(self.x.data_ptr(), self.y.data_ptr(), B, F, st))
+        chk(lib.b200ds_mlp_forward_f32(self.params.data_ptr(), self.x.data_ptr(), B, F, H, self.logits.data_ptr(), st))
+        chk(lib.b200ds_bce_loss_grad(self.logits.data_ptr(), self.y.data_ptr(), B, self.loss.data_ptr(), self.dz.data_ptr(),
+                                     self.counter.data_ptr(), self.bce_sc.data_ptr(), self.bce_sc.numel(), st))
+        if ev_pair:
+            ev_pair[0].record()
+        chk(lib.b200ds_mlp_backward_f32(self.params.data_ptr(), self.x.data_ptr(), self.dz.data_ptr(), B, F, H,
+                                        self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
+        if ev_pair:
+            ev_pair[1].record()
+        chk(lib.b200ds_allreduce_bucket(self.ctx, self.grads.data_ptr(), self.P, st))
+        chk(lib.b200ds_adam_step_counted(self.params.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
+                                         self.Ppad, LR, 0.9, 0.999, 1e-8, self.counter.data_ptr(),
+                                         1.0 / self.world, 0, st))
+
+    dominant = dict(name="mlp_backward_f32_kernel (+finish)", bound="tensor")
+
+    def dominant_flops(self):
+        # algorithmic work of the backward: dW1 2FH, dh 2H, dW2 2H per sample (recompute not counted)
+        return self.B * (2 * self.F * self.H + 4 * self.H)
+
+
+def run_ours(a):
+    import torch.distributed as dist
+
+    from b200ds import _lib, comm
+    lib = _lib.load()
+    le = comm.read_launch_env()
+    world, rank, local = le.world_size, le.rank, le.local_rank
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback); use --impl reference for the CPU arm"
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        comm.init_distributed()
+    wl = WORKLOADS[a.workload]
+    precision = "fp32" if a.precision == "auto" else a.precision
+    ctx = C.c_void_p()
+    nid = comm.exchange_nccl_id(lambda: _nccl_id(lib), le)
+    idbuf = C.create_string_buffer(nid, 128) if nid else None
+    _lib.check(lib.b200ds_ctx_create(local, rank, world, C.cast(idbuf, C.c_void_p) if idbuf else None, C.byref(ctx)))
+    pk = peaks()
+    st = torch.cuda.current_stream().cuda_stream
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    out = {}
+    if a.workload == "tiny":
+        res = bench_tiny(lib, ctx, dev, world, rank, a, barrier)
+        out.update(res)
+    else:
+        ws = WideStep(lib, ctx, dev, wl, world, rank, precision)
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+        for _ in range(max(3, a.warmup)):
+            ws.step(st)
+        barrier()
+        K = a.steps
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        clk = ClockSampler(local)
+        clk.start()
+        wall0 = time.perf_counter()
+        for i in range(K):
+            flush.fill_(i & 0xFF)                 # L2 flush between timed steps, outside the event bracket
+            evs[i][0].record()
+            ws.step(st, kev[i])
+            evs[i][1].record()
+            if i % 8 == 7:
+                clk.sample()
+        clk.sample()
+        barrier()
+        wall = time.perf_counter() - wall0
+        clk.stop()
+        dev_ms = sum(e0.elapsed_time(e1) for e0, e1 in evs)
+        k_ms = sum(e0.elapsed_time(e1) for e0, e1 in kev) / K
+        t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms = float(t)
+        ms_per_step = dev_ms / K
+        value = world * wl["B"] * K / (dev_ms / 1e3)
+        loss_last = float(ws.loss)
+        achieved = ws.dominant_flops() / (k_ms / 1e3) / 1e12
+        roof = dict(bound="tensor", achieved=achieved, peak=pk["tf_sus"], unit="TFLOP/s", frac=achieved / pk["tf_sus"],
+                    traffic=None, kernel=ws.dominant["name"], kernel_ms=k_ms, peak_source=f"{pk['src']} bf16 sustained",
+                    step_frac=step_flops(**wl) / (ms_per_step / 1e3) / 1e12 / pk["tf_sus"])
+        # ---- e2e: the C-ABI host-buffer call, H2D/D2H inside the timed region
+        e2e = bench_e2e(lib, ctx, dev, wl, world, a, barrier)
+        out.update(dict(value=value, ms_per_step=ms_per_step, roofline=roof, e2e=e2e, clocks=clk.summary(),
+                        gpu_launches=K * ws.launches_per_step, wall_s=wall, loss_last=loss_last,
+                        config={"workload": f"{a.workload}: train.py step, F={wl['F']} H={wl['H']}, {wl['B']} samples/GPU/step "
+                                            f"generated on device (Philox4x32-10), Adam, {world} rank(s)",
+                                "per_gpu_batch": wl["B"], "n_features": wl["F"], "hidden": wl["H"], "parallelism": f"dp{world}",
+                                "l2": "256 MiB device buffer rewritten between timed steps, outside the per-step CUDA-event brackets",
+                                "timing": "sum of per-step CUDA-event times on the launching stream, max over ranks"},
+                        dtype="f32" if precision == "fp32" else "bf16"))
+        if not a.no_tiny and rank == 0 and world == 1:
+            try:
+                out["tiny"] = bench_tiny(lib, ctx, dev, 1, 0, a, barrier, brief=True)
+            except Exception as e:      # noqa: BLE001
+                out["tiny"] = {"error": repr(e)}
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        cb = cpu_reference_run(wl if a.workload != "tiny" else WORKLOADS["tiny"], steps=1000 if a.workload == "tiny" else 12,
+                               warmup=1, budget_s=15.0)
+        out["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    elif rank == 0:
+        out["cpu_baseline"] = None
+    _lib.check(lib.b200ds_ctx_destroy(ctx))
+    if rank == 0:
+        line = dict(metric="train_samples_per_sec", value=out.pop("value"), unit="samples/s", n_gpus=world, steps=a.steps,
+                    warmup=max(3, a.warmup), ms_per_step=out.pop("ms_per_step"), higher_is_better=True, scaling="weak",
+                    vs_baseline=None, dtype=out.pop("dtype"), data="synthetic: on-device Philox N(0,1) batches with the label rule "
+                    "of train.py:22-23; weights random-init with nn.Linear's default init in train.py's order",
+                    config=out.pop("config"))
+        line.update(out)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        try:
+            dist.barrier()
+            dist.destroy_process_group()
+        except Exception:       # noqa: BLE001
+            pass
+
+
+def _nccl_id(lib):
+    from b200ds import _lib
+    buf = C.create_string_buffer(128)
+    _lib.check(lib.b200ds_nccl_unique_id(buf))
+    return buf.raw
+
+
+def bench_e2e(lib, ctx, dev, wl, world, a, barrier):
+    """Same step through b200ds_train_step_host: inputs in pinned host memory, loss read
+    back to the host every step."""
+    import torch.distributed as dist
+
+    from b200ds import _lib
+    B, F, H = wl["B"], wl["F"], wl["H"]
+    P = F * H + 2 * H + 1
+    Ppad = (P + 3) // 4 * 4
+    flat = init_flat(F, H)
+    z = lambda n: torch.zeros(n, dtype=torch.float32, device=dev)      # noqa: E731
+    params = z(Ppad); params[:P] = flat.to(dev)
+    grads, m, v, xs, ys, lg, dl, ls = z(Ppad), z(Ppad), z(Ppad), z(B * F), z(B), z(B), z(B), z(1)
+    sc = torch.zeros(max(256, lib.b200ds_train_step_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
+    bufs = _lib.StepBufs(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), xs.data_ptr(), ys.data_ptr(),
+                         lg.data_ptr(), dl.data_ptr(), ls.data_ptr(), sc.data_ptr(), sc.numel())
+    nbuf = 4
+    xh = [torch.randn(B, F).pin_memory() for _ in range(nbuf)]
+    yh = [label_rule(x).contiguous().pin_memory() for x in xh]
+    lh = torch.zeros(1).pin_memory()
+    st = torch.cuda.current_stream().cuda_stream
+    step = 0
+    K = max(3, min(a.steps, 20))
+    for i in range(3):
+        _lib.check(lib.b200ds_train_step_host(ctx, C.byref(bufs), xh[i % nbuf].data_ptr(), yh[i % nbuf].data_ptr(), B, F, H,
+                                              LR, 0.9, 0.999, 1e-8, step, lh.data_ptr(), st))
+        step += 1
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(K):
+        _lib.check(lib.b200ds_train_step_host(ctx, C.byref(bufs), xh[i % nbuf].data_ptr(), yh[i % nbuf].data_ptr(), B, F, H,
+                                              LR, 0.9, 0.999, 1e-8, step, lh.data_ptr(), st))
+        step += 1
+    e1.record()
+    barrier()
+    dt = max(time.perf_counter() - t0, e0.elapsed_time(e1) / 1e3)
+    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return dict(value=world * B * K / float(t), unit="samples/s", h2d_bytes_per_step=4 * (B * F + B), d2h_bytes_per_step=4,
+                steps=K, api="b200ds_train_step_host (C ABI, pinned host x/y in, host loss out, stream sync per step)",
+                loss_last=float(lh))
+
+
+def bench_tiny(lib, ctx, dev, world, rank, a, barrier, brief=False):
+    """The reference's own shape (B=4/rank, F=20, H=64, N=2000): epochs of 500/W steps through
+    the fused kernel(s) on the device-resident dataset; latency-bound, no roofline quoted."""
+    import torch.distributed as dist
+
+    from b200ds import _lib
+    torch.manual_seed(SEED)
+    x = torch.randn(2000, 20)
+    y = label_rule(x)
+    flat = init_flat(20, 64)
+    P, Ppad = 1409, 1412
+    z = lambda n: torch.zeros(n, dtype=torch.float32, device=dev)      # noqa: E731
+    params = z(Ppad); params[:P] = flat.to(dev)
+    grads, m, v = z(Ppad), z(Ppad), z(Ppad)
+    xd, yd = x.to(dev), y.reshape(-1).to(dev)
+    g = torch.Generator(); g.manual_seed(1)
+    order = torch.randperm(2000, generator=g)[rank::world].to(torch.int64).to(dev)      # DistributedSampler-style shard
+    n_steps = (order.numel() + 3) // 4
+    losses = z(n_steps)
+    st = torch.cuda.current_stream().cuda_stream
+    step0 = [0]
+
+    def epoch():
+        if world == 1:
+            _lib.check(lib.b200ds_tiny_train_steps_f32(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), 20, 64,
+                                                       xd.data_ptr(), yd.data_ptr(), order.data_ptr(), order.numel(), 0, 4,
+                                                       n_steps, 1, LR, 0.9, 0.999, 1e-8, step0[0], losses.data_ptr(), st))
+            step0[0] += n_steps
+            return 1
+        for s in range(n_steps):
+            _lib.check(lib.b200ds_tiny_train_steps_f32(params.data_ptr(), grads.data_ptr(), None, None, 20, 64, xd.data_ptr(),
+                                                       yd.data_ptr(), order.data_ptr(), order.numel(), 4 * s, 4, 1, 0,
+                                                       LR, 0.9, 0.999, 1e-8, step0[0], losses.data_ptr() + 4 * s, st))
+            _lib.check(lib.b200ds_allreduce_bucket(ctx, grads.data_ptr(), P, st))
+            step0[0] += 1
+            _lib.check(lib.b200ds_adam_step(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), Ppad,
+                                            LR, 0.9, 0.999, 1e-8, step0[0], 1.0 / world, 0, st))
+        return 2 * n_steps
+    for _ in range(3):
+        epoch()
+    barrier()
+    reps = 5 if brief else max(5, a.steps // 8)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clk = ClockSampler(dev.index)
+    e0.record()
+    launches = 0
+    for _ in range(reps):
+        launches += epoch()
+    e1.record()
+    clk.sample()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t)
+    steps_total = reps * n_steps
+    samples = world * reps * 2000 if world > 1 else reps * 2000
+    res = dict(samples_per_s=samples / (ms / 1e3), us_per_step=1e3 * ms / steps_total, steps=steps_total,
+               launches=launches, epoch_mean_loss=float(losses.double().mean()),
+               note="reference shape B=4/rank F=20 H=64 N=2000; fused one-CTA kernel, device-resident dataset; latency-bound")
+    if brief:
+        return res
+    return dict(value=res["samples_per_s"], ms_per_step=res["us_per_step"] / 1e3, dtype="f32", gpu_launches=launches,
+                clocks=clk.summary(), roofline=None, e2e=None, tiny=res,
+                config={"workload": "tiny: train.py reference shape, F=20 H=64, 4 samples/rank/step, N=2000 resident dataset",
+                        "parallelism": f"dp{world}", "l2": "not flushed: 168 kB working set, latency-bound by design"})
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if rank != 0:
+        return
+    wl = WORKLOADS[a.workload]
+    r = cpu_reference_run(wl, steps=a.steps, warmup=max(1, a.warmup))
+    line = dict(impl="reference", metric="train_samples_per_sec", value=r["value"], unit="samples/s", n_gpus=world,
+                steps=r["steps"], warmup=max(1, a.warmup), ms_per_step=r["ms_per_step"], higher_is_better=True,
+                scaling="weak", vs_baseline=None, dtype="f32",
+                data="synthetic: host torch.randn batches with the label rule of train.py:22-23; nn.Linear default init",
+                config={"workload": f"{a.workload}: train.py step, F={wl['F']} H={wl['H']}, CPU reference path on "
+                                    f"{r['Bs']}-sample slices of the {wl['B']}-sample per-GPU batch",
+                        "per_gpu_batch": wl["B"], "n_features": wl["F"], "hidden": wl["H"], "parallelism": "cpu"},
+                cpu_baseline={k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                e2e=dict(value=r["value"], unit="samples/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                gpu_launches=0)
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)

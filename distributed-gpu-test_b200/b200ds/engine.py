@@ -1,0 +1,322 @@
+"""Engine-style API of the training step: the drop-in for what train.py gets back from
+`deepspeed.initialize(...)` (train.py:87-94) and drives in its loop (train.py:100-125):
+
+    engine.device / engine.train() / engine(x) / engine.backward(loss) / engine.step()
+    / engine.save_checkpoint(dir)
+
+Every arithmetic step is a call into libb200ds.so (include/b200ds.h); torch only owns
+the device memory and the streams.  There is no eager/PyTorch fallback for the step.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import weakref
+
+import torch
+
+from . import _lib, comm
+
+_PRECISIONS = ("fp32", "bf16")
+
+
+def _find_mlp(model: torch.nn.Module):
+    """The path this engine accelerates is SimpleNet (train.py:26-36):
+    Sequential(Linear(F,H), ReLU, Linear(H,1)).  Anything else is out of scope and says so."""
+    seqs = [m for m in model.modules() if isinstance(m, torch.nn.Sequential)]
+    if isinstance(model, torch.nn.Sequential):
+        seqs.insert(0, model)
+    for s in seqs:
+        mods = list(s)
+        if (len(mods) == 3 and isinstance(mods[0], torch.nn.Linear) and isinstance(mods[1], torch.nn.ReLU)
+                and isinstance(mods[2], torch.nn.Linear) and mods[2].out_features == 1
+                and mods[0].out_features == mods[2].in_features
+                and mods[0].bias is not None and mods[2].bias is not None):
+            return mods[0], mods[2]
+    raise NotImplementedError(
+        "b200ds accelerates the train.py model family only: Sequential(Linear(F,H), ReLU, Linear(H,1)) "
+        "(reference train.py:26-36); got %s" % type(model).__name__)
+
+
+def _parse_config(config) -> dict:
+    cfg = dict(config or {})
+    gas = int(cfg.get("gradient_accumulation_steps", 1))
+    if gas != 1:
+        raise NotImplementedError("gradient_accumulation_steps != 1 is outside the reference path (train.py:80)")
+    if bool(cfg.get("fp16", {}).get("enabled", False)):
+        raise NotImplementedError("fp16 is disabled in the reference (train.py:81); use bf16.enabled for the bf16 extension")
+    stage = int(cfg.get("zero_optimization", {}).get("stage", 0))
+    if stage not in (0,):
+        raise NotImplementedError("zero_optimization.stage %d: the reference runs stage 0 (train.py:82)" % stage)
+    precision = "bf16" if bool(cfg.get("bf16", {}).get("enabled", False)) else "fp32"
+    return {"precision": precision, "stage": stage, "train_batch_size": cfg.get("train_batch_size")}
+
+
+class B200Engine:
+    def __init__(self, model, optimizer, config=None, device=None):
+        self.lib = _lib.load()
+        self.cfg = _parse_config(config)
+        self.le = comm.init_distributed()
+        if not torch.cuda.is_available():
+            raise _lib.B200dsError("b200ds needs a CUDA device (sm_100a); there is no CPU path")
+        self.device = torch.device("cuda", self.le.local_rank) if device is None else torch.device(device)
+        torch.cuda.set_device(self.device)
+        self.module = model
+        self.training = True
+        l1, l2 = _find_mlp(model)
+        self.F, self.H = l1.in_features, l1.out_features
+        self.P = self.F * self.H + 2 * self.H + 1
+        self.Ppad = (self.P + 3) // 4 * 4
+        if not isinstance(optimizer, torch.optim.Adam) or isinstance(optimizer, torch.optim.AdamW):
+            raise NotImplementedError("the reference path uses torch.optim.Adam (train.py:85); got %r" % type(optimizer).__name__)
+        if len(optimizer.param_groups) != 1:
+            raise NotImplementedError("one parameter group, as in train.py:85")
+        g = optimizer.param_groups[0]
+        if g.get("weight_decay", 0) != 0 or g.get("amsgrad", False) or g.get("maximize", False):
+            raise NotImplementedError("Adam options beyond lr/betas/eps are outside the reference path (train.py:85)")
+        self.optimizer = optimizer
+        self.global_steps = 0
+
+        # ---- context (communicator, side stream) ----------------------------------
+        ctx = C.c_void_p()
+        nccl_id = comm.exchange_nccl_id(self._make_nccl_id, self.le)
+        idbuf = C.create_string_buffer(nccl_id, _lib.NCCL_ID_BYTES) if nccl_id else None
+        _lib.check(self.lib.b200ds_ctx_create(self.device.index, self.le.rank, self.le.world_size,
+                                              C.cast(idbuf, C.c_void_p) if idbuf else None, C.byref(ctx)), "ctx_create")
+        self.ctx = ctx
+        self._finalizer = weakref.finalize(self, self.lib.b200ds_ctx_destroy, ctx)
+
+        # ---- flat fp32 buffers; the module's parameters become views into `flat` ----
+        dev = self.device
+        self.flat = torch.zeros(self.Ppad, dtype=torch.float32, device=dev)
+        self.grads = torch.zeros(self.Ppad, dtype=torch.float32, device=dev)      # the gradient bucket
+        self.exp_avg = torch.zeros(self.Ppad, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(self.Ppad, dtype=torch.float32, device=dev)
+        o = 0
+        self._views = []
+        for p in (l1.weight, l1.bias, l2.weight, l2.bias):
+            n = p.numel()
+            self.flat[o:o + n].copy_(p.detach().reshape(-1).to(torch.float32))
+            p.data = self.flat[o:o + n].view(p.shape)
+            p.grad = None
+            self._views.append((p, o, n))
+            o += n
+        assert o == self.P
+        stream = _lib.current_stream()
+        _lib.check(self.lib.b200ds_broadcast_params(self.ctx, self.flat.data_ptr(), self.P, stream), "broadcast_params")
+        for p, off, n in self._views:     # keep optimizer.state_dict() meaningful
+            optimizer.state[p] = {"step": torch.tensor(0.0), "exp_avg": self.exp_avg[off:off + n].view(p.shape),
+                                  "exp_avg_sq": self.exp_avg_sq[off:off + n].view(p.shape)}
+        self._x = None
+        self._logits = None
+        self._scratch = None
+        self._bce_scratch = torch.zeros(self.lib.b200ds_bce_scratch_bytes(0), dtype=torch.uint8, device=dev)
+
+    # ------------------------------------------------------------------ helpers
+    def _make_nccl_id(self) -> bytes:
+        buf = C.create_string_buffer(_lib.NCCL_ID_BYTES)
+        _lib.check(self.lib.b200ds_nccl_unique_id(buf), "nccl_unique_id")
+        return buf.raw
+
+    def _hyper(self):
+        g = self.optimizer.param_groups[0]
+        b1, b2 = g["betas"]
+        return float(g["lr"]), float(b1), float(b2), float(g["eps"])
+
+    def _scratch_for(self, nbytes: int) -> torch.Tensor:
+        if self._scratch is None or self._scratch.numel() < nbytes:
+            self._scratch = torch.zeros(max(nbytes, 256), dtype=torch.uint8, device=self.device)
+        return self._scratch
+
+    # ------------------------------------------------------------------ train.py:100
+    def train(self, mode: bool = True):
+        self.training = mode
+        self.module.train(mode)
+        return self
+
+    def eval(self):
+        return self.train(False)
+
+    # ------------------------------------------------------------------ train.py:107
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        return self.forward(x)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if x.device != self.device or x.dtype != torch.float32 or x.dim() != 2 or x.shape[1] != self.F:
+            raise ValueError("engine(x): expected a float32 [B,%d] tensor on %s, got %s %s on %s"
+                             % (self.F, self.device, x.dtype, tuple(x.shape), x.device))
+        x = x.contiguous()
+        B = x.shape[0]
+        logits = torch.empty((B, 1), dtype=torch.float32, device=self.device)
+        _lib.check(self.lib.b200ds_mlp_forward_f32(self.flat.data_ptr(), x.data_ptr(), B, self.F, self.H,
+                                                   logits.data_ptr(), _lib.current_stream()), "mlp_forward_f32")
+        self._x = x
+        self._logits = logits
+        logits._b200ds_engine = weakref.ref(self)
+        if self.training:
+            logits.requires_grad_(True)     # lets a foreign torch criterion reach d(loss)/d(logits)
+        return logits
+
+    # ------------------------------------------------------------------ train.py:113
+    def backward(self, loss: torch.Tensor):
+        if self._x is None:
+            raise RuntimeError("engine.backward(loss) called before engine(x)")
+        dlogits = getattr(loss, "_b200ds_dlogits", None)
+        if dlogits is None:
+            # user-side loss written in torch (train.py:96 uses nn.BCEWithLogitsLoss): take its
+            # derivative w.r.t. our logits from autograd, everything below is ours again.
+            (dlogits,) = torch.autograd.grad(loss, self._logits)
+            dlogits = dlogits.contiguous()
+        B = self._x.shape[0]
+        need = self.lib.b200ds_mlp_backward_f32_scratch_bytes(B, self.F, self.H)
+        scratch = self._scratch_for(need)
+        stream = _lib.current_stream()
+        _lib.check(self.lib.b200ds_mlp_backward_f32(self.flat.data_ptr(), self._x.data_ptr(), dlogits.data_ptr(), B,
+                                                    self.F, self.H, self.grads.data_ptr(), scratch.data_ptr(),
+                                                    scratch.numel(), stream), "mlp_backward_f32")
+        # DeepSpeed stage 0: gradients are averaged across ranks before backward() returns
+        _lib.check(self.lib.b200ds_allreduce_bucket(self.ctx, self.grads.data_ptr(), self.P, stream), "allreduce_bucket")
+
+    # ------------------------------------------------------------------ train.py:114
+    def step(self):
+        lr, b1, b2, eps = self._hyper()
+        self.global_steps += 1
+        scale = 1.0 / self.le.world_size if self.le.world_size > 1 else 1.0
+        _lib.check(self.lib.b200ds_adam_step(self.flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
+                                             self.exp_avg_sq.data_ptr(), self.Ppad, lr, b1, b2, eps, self.global_steps,
+                                             scale, 0, _lib.current_stream()), "adam_step")
+        self._x = None
+        self._logits = None
+
+    # ------------------------------------------------------------------ fused fast paths (additions)
+    def supports_fused_steps(self, batch: int) -> bool:
+        return self.F <= 32 and self.H <= 256 and 1 <= batch <= 32
+
+    def fused_steps(self, x_all: torch.Tensor, y_all: torch.Tensor, order: torch.Tensor, first: int,
+                    batch: int, n_steps: int, losses: torch.Tensor | None = None) -> torch.Tensor:
+        """Run `n_steps` whole training steps of train.py:104-117 on device-resident data:
+        step s uses rows order[first + s*batch : first + (s+1)*batch] of (x_all, y_all).
+        world == 1: one launch for all steps.  world > 1: per step one fused
+        forward/loss/backward launch, the bucket all-reduce and the Adam launch.
+        Returns the per-step losses (float32 [n_steps], on device)."""
+        if not self.supports_fused_steps(batch):
+            raise ValueError("fused_steps: shape outside the tiny class (F<=32, H<=256, batch<=32)")
+        if losses is None:
+            losses = torch.empty(n_steps, dtype=torch.float32, device=self.device)
+        lr, b1, b2, eps = self._hyper()
+        stream = _lib.current_stream()
+        y_flat = y_all.reshape(-1)
+        if self.le.world_size == 1:
+            done = 0
+            per_launch = max(1, 8192 // batch)
+            while done < n_steps:
+                k = min(per_launch, n_steps - done)
+                _lib.check(self.lib.b200ds_tiny_train_steps_f32(
+                    self.flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(),
+                    self.F, self.H, x_all.data_ptr(), y_flat.data_ptr(), order.data_ptr(), order.numel(),
+                    first + done * batch, batch, k, 1, lr, b1, b2, eps, self.global_steps,
+                    losses.data_ptr() + 4 * done, stream), "tiny_train_steps_f32")
+                self.global_steps += k
+                done += k
+        else:
+            scale = 1.0 / self.le.world_size
+            for s in range(n_steps):
+                _lib.check(self.lib.b200ds_tiny_train_steps_f32(
+                    self.flat.data_ptr(), self.grads.data_ptr(), None, None, self.F, self.H, x_all.data_ptr(),
+                    y_flat.data_ptr(), order.data_ptr(), order.numel(), first + s * batch, batch, 1, 0,
+                    lr, b1, b2, eps, self.global_steps, losses.data_ptr() + 4 * s, stream), "tiny_train_steps_f32")
+                _lib.check(self.lib.b200ds_allreduce_bucket(self.ctx, self.grads.data_ptr(), self.P, stream), "allreduce_bucket")
+                self.global_steps += 1
+                _lib.check(self.lib.b200ds_adam_step(self.flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
+                                                     self.exp_avg_sq.data_ptr(), self.Ppad, lr, b1, b2, eps,
+                                                     self.global_steps, scale, 0, stream), "adam_step")
+        return losses
+
+    def make_host_step(self, batch: int):
+        """Pre-allocates what b200ds_train_step_host borrows and returns f(x_host, y_host,
+        loss_host) -> None, one end-to-end step over (pinned) host buffers."""
+        dev = self.device
+        nbytes = self.lib.b200ds_train_step_scratch_bytes(batch, self.F, self.H)
+        keep = {
+            "x": torch.empty(batch * self.F, dtype=torch.float32, device=dev),
+            "y": torch.empty(batch, dtype=torch.float32, device=dev),
+            "z": torch.empty(batch, dtype=torch.float32, device=dev),
+            "dz": torch.empty(batch, dtype=torch.float32, device=dev),
+            "loss": torch.zeros(1, dtype=torch.float32, device=dev),
+            "scratch": torch.zeros(max(nbytes, 256), dtype=torch.uint8, device=dev),
+        }
+        bufs = _lib.StepBufs(self.flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
+                             self.exp_avg_sq.data_ptr(), keep["x"].data_ptr(), keep["y"].data_ptr(),
+                             keep["z"].data_ptr(), keep["dz"].data_ptr(), keep["loss"].data_ptr(),
+                             keep["scratch"].data_ptr(), keep["scratch"].numel())
+
+        def host_step(x_host: torch.Tensor, y_host: torch.Tensor, loss_host: torch.Tensor, _keep=keep):
+            lr, b1, b2, eps = self._hyper()
+            _lib.check(self.lib.b200ds_train_step_host(self.ctx, C.byref(bufs), x_host.data_ptr(), y_host.data_ptr(),
+                                                       x_host.shape[0], self.F, self.H, lr, b1, b2, eps,
+                                                       self.global_steps, loss_host.data_ptr(),
+                                                       _lib.current_stream()), "train_step_host")
+            self.global_steps += 1
+        return host_step
+
+    # ------------------------------------------------------------------ train.py:125
+    def save_checkpoint(self, save_dir: str, tag: str | None = None, client_state: dict | None = None):
+        """Collective like DeepSpeed's: every rank calls; rank 0 writes
+        <save_dir>/<tag>/mp_rank_00_model_states.pt and <save_dir>/latest, then all ranks
+        meet at a barrier.  [DS-UNVERIFIED layout, see SURVEY 8f-1]"""
+        tag = tag or f"global_step{self.global_steps}"
+        if self.le.rank == 0:
+            d = os.path.join(save_dir, tag)
+            os.makedirs(d, exist_ok=True)
+            flat = self.flat.detach().cpu()
+            sd = {}
+            names = dict((id(p), n) for n, p in self.module.named_parameters())
+            for p, off, n in self._views:
+                sd[names[id(p)]] = flat[off:off + n].view(p.shape).clone()
+            state = {
+                "module": sd,
+                "optimizer": {"exp_avg": self.exp_avg[: self.P].cpu(), "exp_avg_sq": self.exp_avg_sq[: self.P].cpu(),
+                              "step": self.global_steps, "param_groups": [
+                                  {k: v for k, v in self.optimizer.param_groups[0].items() if k != "params"}]},
+                "global_steps": self.global_steps,
+                "dp_world_size": self.le.world_size,
+                "client_state": client_state or {},
+            }
+            torch.save(state, os.path.join(d, "mp_rank_00_model_states.pt"))
+            with open(os.path.join(save_dir, "latest"), "w") as f:
+                f.write(tag)
+        _lib.check(self.lib.b200ds_barrier(self.ctx), "barrier")
+        return True
+
+    def destroy(self):
+        self._finalizer()
+
+
+class BCEWithLogitsLoss:
+    """criterion(logits, y) (train.py:96,112) as ONE fused kernel that also produces
+    d(loss)/d(logits); the result is an ordinary 0-dim CUDA tensor (`.item()` works,
+    train.py:115) that carries the gradient for engine.backward(loss)."""
+
+    def __init__(self, reduction: str = "mean"):
+        if reduction != "mean":
+            raise NotImplementedError("the reference uses the default mean reduction (train.py:96)")
+        self.lib = _lib.load()
+        self._scratch = {}
+
+    def __call__(self, logits: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        if logits.shape != target.shape:
+            raise ValueError(f"Target size ({tuple(target.shape)}) must be the same as input size ({tuple(logits.shape)})")
+        z = logits.detach().contiguous()
+        y = target.detach().to(torch.float32).contiguous()
+        n = z.numel()
+        out = torch.empty(1, dtype=torch.float32, device=z.device)
+        dz = torch.empty(z.shape, dtype=torch.float32, device=z.device)
+        key = z.device.index
+        if key not in self._scratch:
+            self._scratch[key] = torch.zeros(self.lib.b200ds_bce_scratch_bytes(n), dtype=torch.uint8, device=z.device)
+        sc = self._scratch[key]
+        _lib.check(self.lib.b200ds_bce_loss_grad(z.data_ptr(), y.data_ptr(), n, out.data_ptr(), dz.data_ptr(), None,
+                                                 sc.data_ptr(), sc.numel(), _lib.current_stream()), "bce_loss_grad")
+        loss = out.view(())
+        loss._b200ds_dlogits = dz
+        return loss

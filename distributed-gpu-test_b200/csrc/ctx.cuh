@@ -1,0 +1,30 @@
+// The per-process context: what deepspeed.init_distributed() + set_device leave behind
+// in the reference (train.py:59-61) -- a device binding and a communicator -- plus the
+// side stream and events the bucket all-reduce is ordered with.
+#pragma once
+#include "common.cuh"
+#include <nccl.h>
+
+struct b200ds_ctx {
+  int device = 0, rank = 0, world = 1;
+  ncclComm_t comm = nullptr;
+  cudaStream_t side = nullptr;       // all-reduce stream (non-blocking)
+  cudaEvent_t ev_ready = nullptr;    // bucket complete on the caller's stream
+  cudaEvent_t ev_done = nullptr;     // all-reduce complete on the side stream
+  int64_t* iota = nullptr;           // device [32] = 0..31, identity order for the host-buffer step
+  float* barrier_word = nullptr;     // device scratch for b200ds_barrier
+};
+
+namespace b200ds {
+// NCCL is bound at run time (dlopen of the libnccl.so.2 torch already loaded, else the
+// system one) so that the library loads on machines without NCCL when world == 1.
+struct NcclApi {
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*);
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int);
+  ncclResult_t (*CommDestroy)(ncclComm_t);
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  const char* (*GetErrorString)(ncclResult_t);
+};
+const NcclApi* nccl_api();   // nullptr (+ error string set) when NCCL cannot be loaded
+}  // namespace b200ds

@@ -1,0 +1,65 @@
+// End-to-end training step over HOST buffers: the whole of train.py:104-115 for one batch
+// behind one C call (H2D copies, forward, loss, backward, all-reduce, Adam, loss D2H,
+// sync).  This is the call bench.py times for its `e2e` figure.
+#include "ctx.cuh"
+
+using namespace b200ds;
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static bool tiny_class(int64_t batch, int F, int H) { return F <= 32 && H <= 256 && batch <= 32; }
+
+extern "C" {
+
+size_t b200ds_train_step_scratch_bytes(int64_t batch, int n_features, int hidden) {
+  return align_up(b200ds_bce_scratch_bytes(batch), 256) +
+         align_up(b200ds_mlp_backward_f32_scratch_bytes(batch, n_features, hidden), 256);
+}
+
+int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* b,
+                           const float* x_host, const float* y_host, int64_t batch,
+                           int n_features, int hidden, double lr, double beta1, double beta2,
+                           double eps, int64_t step0, float* loss_host, uintptr_t stream) {
+  B200_REQUIRE(ctx && b && x_host && y_host && loss_host, "train_step_host: null pointer");
+  B200_REQUIRE(batch > 0 && n_features >= 1 && hidden >= 1, "train_step_host: bad shape");
+  B200_REQUIRE(b->params && b->grads && b->exp_avg && b->exp_avg_sq && b->x_stage && b->y_stage && b->loss,
+               "train_step_host: missing device buffer");
+  cudaStream_t s = as_stream(stream);
+  const Layout L{n_features, hidden};
+  const int64_t P = L.count();
+  const int64_t Ppad = (P + 3) / 4 * 4;
+  int rc;
+  B200_CUDA(cudaMemcpyAsync(b->x_stage, x_host, sizeof(float) * batch * n_features, cudaMemcpyHostToDevice, s));
+  B200_CUDA(cudaMemcpyAsync(b->y_stage, y_host, sizeof(float) * batch, cudaMemcpyHostToDevice, s));
+  const float scale = ctx->world > 1 ? (float)(1.0 / ctx->world) : 1.f;
+  if (tiny_class(batch, n_features, hidden)) {
+    const int fused_adam = ctx->world == 1;
+    rc = b200ds_tiny_train_steps_f32(b->params, b->grads, b->exp_avg, b->exp_avg_sq, n_features, hidden,
+                                     b->x_stage, b->y_stage, ctx->iota, batch, 0, (int)batch, 1, fused_adam,
+                                     lr, beta1, beta2, eps, step0, b->loss, stream);
+    if (rc) return rc;
+    if (!fused_adam) {
+      if ((rc = b200ds_allreduce_bucket(ctx, b->grads, P, stream))) return rc;
+      if ((rc = b200ds_adam_step(b->params, b->grads, b->exp_avg, b->exp_avg_sq, Ppad, lr, beta1, beta2, eps,
+                                 step0 + 1, scale, 0, stream))) return rc;
+    }
+  } else {
+    B200_REQUIRE(b->logits && b->dlogits, "train_step_host: logits/dlogits buffers required");
+    size_t need = b200ds_train_step_scratch_bytes(batch, n_features, hidden);
+    B200_REQUIRE(b->scratch && b->scratch_bytes >= need, "train_step_host: scratch too small (%zu < %zu)", b->scratch_bytes, need);
+    char* sc = reinterpret_cast<char*>(b->scratch);
+    size_t bce_bytes = align_up(b200ds_bce_scratch_bytes(batch), 256);
+    if ((rc = b200ds_mlp_forward_f32(b->params, b->x_stage, batch, n_features, hidden, b->logits, stream))) return rc;
+    if ((rc = b200ds_bce_loss_grad(b->logits, b->y_stage, batch, b->loss, b->dlogits, nullptr, sc, bce_bytes, stream))) return rc;
+    if ((rc = b200ds_mlp_backward_f32(b->params, b->x_stage, b->dlogits, batch, n_features, hidden, b->grads,
+                                      sc + bce_bytes, b->scratch_bytes - bce_bytes, stream))) return rc;
+    if ((rc = b200ds_allreduce_bucket(ctx, b->grads, P, stream))) return rc;
+    if ((rc = b200ds_adam_step(b->params, b->grads, b->exp_avg, b->exp_avg_sq, Ppad, lr, beta1, beta2, eps,
+                               step0 + 1, scale, 0, stream))) return rc;
+  }
+  B200_CUDA(cudaMemcpyAsync(loss_host, b->loss, sizeof(float), cudaMemcpyDeviceToHost, s));
+  B200_CUDA(cudaStreamSynchronize(s));
+  return B200DS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,180 @@
+/* b200ds.h -- C ABI of libb200ds.so: the B200 (sm_100a) implementation of the one
+ * data-parallel hot path of dashabalashova/distributed-gpu-test, the training step of
+ * train.py (forward, BCE-with-logits loss, backward, gradient all-reduce, Adam).
+ *
+ * The reference has no FFI of its own: train.py reaches its arithmetic through the
+ * Python APIs of torch and DeepSpeed.  Each entry point below therefore cites the
+ * reference CALL SITE (file:line into the reference repo) whose work it replaces; the
+ * Python shim `b200ds` (distributed-gpu-test_b200/b200ds) mirrors the DeepSpeed names
+ * train.py uses and binds these symbols with ctypes.
+ *
+ * Conventions
+ *   - every pointer named *_dev / documented "device" is a raw CUDA device pointer
+ *     (tensor.data_ptr()); the caller (torch) owns the memory and keeps it alive until
+ *     the stream work that uses it has finished.  The library allocates nothing on the
+ *     step path; kernels that need scratch take it from the caller
+ *     (see the *_scratch_bytes queries).  A context owns only its side stream, events,
+ *     pinned mailbox and NCCL communicator.
+ *   - `stream` is a cudaStream_t passed as uintptr_t (0 = legacy default stream).  All
+ *     work is stream-ordered; no entry point synchronises the host unless it says so.
+ *   - return value: 0 on success, otherwise one of B200DS_ERR_*; b200ds_last_error()
+ *     returns a thread-local message.  Nothing throws across this boundary.
+ *   - one caller thread per context.
+ *   - flat parameter layout (fp32), the order of SimpleNet.parameters() (train.py:29-33):
+ *       [ W1 (H*F, row-major [H,F]) | b1 (H) | W2 (H) | b2 (1) ],  P = H*F + 2H + 1.
+ *     Gradients, Adam exp_avg and exp_avg_sq use the same layout.
+ */
+#ifndef B200DS_H_
+#define B200DS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B200DS_API __attribute__((visibility("default")))
+#else
+#define B200DS_API
+#endif
+
+#define B200DS_OK 0
+#define B200DS_ERR_ARG 1      /* bad argument / unsupported shape */
+#define B200DS_ERR_CUDA 2     /* a CUDA runtime call failed */
+#define B200DS_ERR_NCCL 3     /* an NCCL call failed */
+#define B200DS_ERR_STATE 4    /* call made in the wrong state (e.g. no communicator) */
+
+#define B200DS_NCCL_ID_BYTES 128
+
+typedef struct b200ds_ctx b200ds_ctx;
+
+/* ---- library ------------------------------------------------------------------- */
+B200DS_API const char* b200ds_last_error(void);
+B200DS_API int b200ds_version(void);                       /* 10000*major + 100*minor + patch */
+B200DS_API int b200ds_device_sm_count(int device, int* sm_count);
+
+/* ---- context: replaces deepspeed.init_distributed() + set_device (train.py:59-61) --
+ * rank/world come from the launcher's RANK/WORLD_SIZE (train.py:56-57).  world == 1
+ * needs no id.  For world > 1 rank 0 calls b200ds_nccl_unique_id and publishes the 128
+ * bytes (the shim uses the torch TCP store at MASTER_ADDR:MASTER_PORT); every rank then
+ * calls b200ds_ctx_create with the same bytes.  Collective: all ranks must call. */
+B200DS_API int b200ds_nccl_unique_id(void* id128);
+B200DS_API int b200ds_ctx_create(int device, int rank, int world, const void* nccl_id128, b200ds_ctx** out);
+B200DS_API int b200ds_ctx_destroy(b200ds_ctx* ctx);
+B200DS_API int b200ds_ctx_info(const b200ds_ctx* ctx, int* device, int* rank, int* world);
+
+/* ---- synthetic data: replaces make_synthetic_data (train.py:19-24) for the
+ * generated-batch configs.  Philox4x32-10 + Box-Muller with the element mapping of
+ * torch.randn(numel, device='cuda') under (seed, offset): bit-identical to it on the
+ * same GPU model.  *offset_advance (host, may be NULL) receives how far the generator
+ * offset moves, as torch's CUDA generator would. */
+B200DS_API int b200ds_philox_normal(float* x_dev, int64_t numel, uint64_t seed, uint64_t offset,
+                         uint64_t* offset_advance, uintptr_t stream);
+/* y[b] = 1 if sum_{j < F/2} x[b,j] > 0 else 0   (train.py:22-23) */
+B200DS_API int b200ds_label_rule(const float* x_dev, float* y_dev, int64_t batch, int n_features,
+                      uintptr_t stream);
+/* Batch gather from the device-resident dataset: replaces TensorDataset indexing +
+ * default_collate + .to(device) (train.py:65,74,104-106).  idx_dev: int64 [batch]. */
+B200DS_API int b200ds_gather_batch(const float* x_all_dev, const float* y_all_dev, const int64_t* idx_dev,
+                        int64_t batch, int n_features, float* x_out_dev, float* y_out_dev,
+                        uintptr_t stream);
+
+/* ---- fp32 step, one kernel per engine call ---------------------------------------- */
+/* model_engine(batch_x) (train.py:107 -> SimpleNet.forward, train.py:35-36):
+ * logits[b] = relu(x[b,:] W1^T + b1) . W2 + b2.  x: [batch,F] fp32, logits: [batch]. */
+B200DS_API int b200ds_mlp_forward_f32(const float* params_dev, const float* x_dev, int64_t batch,
+                           int n_features, int hidden, float* logits_dev, uintptr_t stream);
+
+/* criterion(logits, y) (train.py:96,112) fused with the first node of
+ * model_engine.backward (train.py:113): loss = mean_b[(1-y) z - logsigmoid(z)],
+ * dlogits[b] = (sigmoid(z) - y)/batch.  loss_dev: 1 float.  dlogits_dev may be NULL.
+ * step_counter_dev (may be NULL): uint64 incremented by one (Adam's t, read by
+ * b200ds_adam_step_counted).  scratch: b200ds_bce_scratch_bytes(batch) bytes, device. */
+B200DS_API size_t b200ds_bce_scratch_bytes(int64_t batch);
+B200DS_API int b200ds_bce_loss_grad(const float* logits_dev, const float* y_dev, int64_t batch,
+                         float* loss_dev, float* dlogits_dev, uint64_t* step_counter_dev,
+                         void* scratch_dev, size_t scratch_bytes, uintptr_t stream);
+
+/* model_engine.backward(loss) up to the all-reduce (train.py:113): recomputes the hidden
+ * activation, writes dW1, db1, dW2, db2 into grads_dev (flat layout, overwritten).
+ * No dx is formed (the input does not require grad).  F <= 256 on this path. */
+B200DS_API size_t b200ds_mlp_backward_f32_scratch_bytes(int64_t batch, int n_features, int hidden);
+B200DS_API int b200ds_mlp_backward_f32(const float* params_dev, const float* x_dev, const float* dlogits_dev,
+                            int64_t batch, int n_features, int hidden, float* grads_dev,
+                            void* scratch_dev, size_t scratch_bytes, uintptr_t stream);
+
+/* ---- gradient exchange: the all-reduce inside model_engine.backward (train.py:113,
+ * DeepSpeed stage 0, ds_config train.py:78-83).  SUM over ranks of bucket_dev[0..n) in
+ * place with ncclAllReduce on the context's side stream: the side stream waits for the
+ * work already enqueued on `stream`, and `stream` then waits for the all-reduce, so the
+ * caller's ordering is preserved without a host sync.  The 1/world scale is NOT applied
+ * here; pass grad_scale = 1/world to b200ds_adam_step.  world == 1: no-op. */
+B200DS_API int b200ds_allreduce_bucket(b200ds_ctx* ctx, float* bucket_dev, int64_t n, uintptr_t stream);
+/* Parameter broadcast from rank 0 done by deepspeed.initialize (train.py:87-93). */
+B200DS_API int b200ds_broadcast_params(b200ds_ctx* ctx, float* params_dev, int64_t n, uintptr_t stream);
+/* dist.barrier() at teardown (train.py:134): host-blocking. */
+B200DS_API int b200ds_barrier(b200ds_ctx* ctx);
+
+/* ---- optimizer: model_engine.step() (train.py:114) = torch.optim.Adam.step with the
+ * defaults of train.py:85 (no weight decay, no amsgrad), then gradients cleared.
+ *   g = grad*grad_scale; m += (g-m)(1-b1); v = b2 v + (1-b2) g g;
+ *   p -= (lr/(1-b1^t)) * m / (sqrt(v)/sqrt(1-b2^t) + eps)
+ * `step` is t AFTER the increment (1 for the first update).  n must cover the flat
+ * buffers; buffers must be 16-byte aligned (128-bit accesses).  zero_grad != 0 clears
+ * grads_dev in the same pass. */
+B200DS_API int b200ds_adam_step(float* params_dev, float* grads_dev, float* exp_avg_dev, float* exp_avg_sq_dev,
+                     int64_t n, double lr, double beta1, double beta2, double eps, int64_t step,
+                     float grad_scale, int zero_grad, uintptr_t stream);
+/* Same, but t is read from a device counter (graph-replayable; see b200ds_bce_loss_grad). */
+B200DS_API int b200ds_adam_step_counted(float* params_dev, float* grads_dev, float* exp_avg_dev,
+                             float* exp_avg_sq_dev, int64_t n, double lr, double beta1, double beta2,
+                             double eps, const uint64_t* step_counter_dev, float grad_scale,
+                             int zero_grad, uintptr_t stream);
+
+/* ---- fused tiny-shape step (train.py:104-117 in one launch) ------------------------
+ * For the reference's own shape class (F <= 32, H <= 1024, per-step batch <= 32): one CTA
+ * keeps the 1409 parameters and their Adam state in registers and runs `n_steps`
+ * consecutive training steps: gather rows order_dev[s*batch .. ) of the resident
+ * dataset, forward, loss, backward, and -- when apply_adam != 0 (world == 1) -- the Adam
+ * update.  With apply_adam == 0, n_steps must be 1 and the gradients are written to
+ * grads_dev for b200ds_allreduce_bucket + b200ds_adam_step.
+ *   order_dev : int64 [n_order] sample indices of this rank for the epoch
+ *   first     : index into order_dev of the first sample of the first step
+ *   losses_dev: float [n_steps], the per-step loss (what loss.item() returns, train.py:115)
+ *   step0     : Adam t before the first of these steps.
+ * The ragged last batch (train.py:74, drop_last=False) is handled (mean over what is left). */
+B200DS_API int b200ds_tiny_train_steps_f32(float* params_dev, float* grads_dev, float* exp_avg_dev,
+                                float* exp_avg_sq_dev, int n_features, int hidden,
+                                const float* x_all_dev, const float* y_all_dev,
+                                const int64_t* order_dev, int64_t n_order, int64_t first,
+                                int batch, int n_steps, int apply_adam, double lr, double beta1,
+                                double beta2, double eps, int64_t step0, float* losses_dev,
+                                uintptr_t stream);
+
+/* ---- end-to-end step with HOST buffers (what bench.py's `e2e` times) ---------------
+ * One call = train.py:104-115 for one batch: H2D of x,y from (pinned) host memory,
+ * forward, loss, backward, all-reduce, Adam (t = step0 + 1), D2H of the loss, and a
+ * stream synchronise (this is the one entry point that blocks the host, as loss.item()
+ * does at train.py:115).  Shapes inside the tiny class (F <= 32, H <= 256, batch <= 32)
+ * take the fused one-launch kernel, others the per-stage fp32 kernels.
+ * The caller supplies every device buffer in `bufs` (all borrowed, fp32):
+ *   scratch: b200ds_train_step_scratch_bytes(...) bytes, zeroed once by the caller. */
+typedef struct b200ds_step_bufs {
+  float* params;  float* grads;  float* exp_avg;  float* exp_avg_sq;   /* flat, length padded to 4 */
+  float* x_stage; float* y_stage;          /* [batch*F], [batch] device staging */
+  float* logits;  float* dlogits;          /* [batch] */
+  float* loss;                             /* 1 float */
+  void* scratch;  size_t scratch_bytes;
+} b200ds_step_bufs;
+B200DS_API size_t b200ds_train_step_scratch_bytes(int64_t batch, int n_features, int hidden);
+B200DS_API int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* bufs,
+                           const float* x_host, const float* y_host, int64_t batch,
+                           int n_features, int hidden, double lr, double beta1, double beta2,
+                           double eps, int64_t step0, float* loss_host, uintptr_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DS_H_ */

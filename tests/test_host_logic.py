@@ -1,0 +1,75 @@
+"""Host-side logic of the drop-in: launcher environment, config handling, CLI."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from b200ds import comm
+from b200ds import engine as eng
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_env_torchrun():
+    le = comm.read_launch_env({"RANK": "5", "LOCAL_RANK": "1", "WORLD_SIZE": "8", "MASTER_ADDR": "10.0.0.1", "MASTER_PORT": "12345"})
+    assert (le.rank, le.local_rank, le.world_size, le.master_addr, le.master_port, le.source) == (5, 1, 8, "10.0.0.1", 12345, "torchrun")
+
+
+def test_env_slurm_fallback():
+    le = comm.read_launch_env({"SLURM_PROCID": "3", "SLURM_LOCALID": "3", "SLURM_NTASKS": "16", "SLURM_JOB_NODELIST": "gpu[03-06,09]"})
+    assert (le.rank, le.local_rank, le.world_size, le.master_addr, le.master_port, le.source) == (3, 3, 16, "gpu03", 12345, "slurm")
+    assert comm._first_host("nodeA,nodeB") == "nodeA"
+    assert comm._first_host("n[7,9-12]") == "n7"
+
+
+def test_env_single_defaults():
+    le = comm.read_launch_env({})
+    assert (le.rank, le.local_rank, le.world_size, le.source) == (0, 0, 1, "single")
+
+
+def test_config_parsing():
+    ok = eng._parse_config({"train_batch_size": 64, "gradient_accumulation_steps": 1, "fp16": {"enabled": False},
+                            "zero_optimization": {"stage": 0}})           # train.py:78-83
+    assert ok["precision"] == "fp32" and ok["stage"] == 0
+    assert eng._parse_config({"bf16": {"enabled": True}})["precision"] == "bf16"
+    for bad in ({"gradient_accumulation_steps": 2}, {"fp16": {"enabled": True}}, {"zero_optimization": {"stage": 3}}):
+        with pytest.raises(NotImplementedError):
+            eng._parse_config(bad)
+
+
+def test_model_family_detection():
+    net = torch.nn.Sequential(torch.nn.Linear(20, 64), torch.nn.ReLU(), torch.nn.Linear(64, 1))
+
+    class Wrap(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.net = net
+
+    l1, l2 = eng._find_mlp(Wrap())
+    assert (l1.in_features, l1.out_features, l2.out_features) == (20, 64, 1)
+    with pytest.raises(NotImplementedError):
+        eng._find_mlp(torch.nn.Sequential(torch.nn.Linear(20, 64), torch.nn.Tanh(), torch.nn.Linear(64, 1)))
+    with pytest.raises(NotImplementedError):
+        eng._find_mlp(torch.nn.Linear(3, 1))
+
+
+def test_cli_matches_reference_defaults(golden):
+    sys.path.insert(0, ROOT)
+    import importlib
+    train = importlib.import_module("train")
+    a = train.cli([])
+    assert [a.train_batch_size, a.epochs, a.seed] == list(golden["cli_defaults"])
+    assert a.lr == float(golden["cli_lr"][0]) and a.save_dir == "ds_checkpoints"
+    # launcher-injected flags are swallowed (slurm_train.sbatch:27-28, torch.distributed.launch)
+    b = train.cli(["--distributed-backend", "nccl", "--deepspeed", "--local-rank=3", "--epochs", "2"])
+    assert b.epochs == 2
+
+
+def test_train_py_fails_loudly_without_gpu():
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "train.py"), "--epochs", "1"], capture_output=True, text=True,
+                       env={k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")})
+    assert r.returncode != 0 and "Epoch" not in r.stdout
