@@ -57,6 +57,14 @@ PROTOTYPES = {
     "b200ds_tiny_train_steps_f32": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr,
                                               c_i64, c_i64, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double,
                                               C.c_double, C.c_double, c_i64, c_ptr, c_stream]),
+    "b200ds_tc_supported": (C.c_int, [c_i64, C.c_int, C.c_int]),
+    "b200ds_tc_xq_bytes": (C.c_size_t, [c_i64]),
+    "b200ds_tc_wq_bytes": (C.c_size_t, [C.c_int]),
+    "b200ds_pack_x_bf16": (C.c_int, [c_ptr, c_i64, C.c_int, c_ptr, c_stream]),
+    "b200ds_pack_params_bf16": (C.c_int, [c_ptr, C.c_int, C.c_int, c_ptr, c_stream]),
+    "b200ds_mlp_forward_tc": (C.c_int, [c_ptr, c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_stream]),
+    "b200ds_mlp_backward_tc_scratch_bytes": (C.c_size_t, [c_i64, C.c_int, C.c_int]),
+    "b200ds_mlp_backward_tc": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_ptr, C.c_size_t, c_stream]),
     "b200ds_train_step_scratch_bytes": (C.c_size_t, [c_i64, C.c_int, C.c_int]),
     "b200ds_train_step_host": (C.c_int, [c_ptr, C.POINTER(StepBufs), c_ptr, c_ptr, c_i64, C.c_int, C.c_int,
                                          C.c_double, C.c_double, C.c_double, C.c_double, c_i64, c_ptr, c_stream]),

@@ -153,6 +153,40 @@ B200DS_API int b200ds_tiny_train_steps_f32(float* params_dev, float* grads_dev, 
                                 double beta2, double eps, int64_t step0, float* losses_dev,
                                 uintptr_t stream);
 
+/* ---- bf16 tensor-core path (tcgen05.mma / TMEM / TMA) for the widened model ----------
+ * BASELINE config 4 (H = 4096..8192, 64K samples per GPU).  The reference has no bf16
+ * path (train.py:81 disables fp16); semantics defined by the build: GEMM operands rounded
+ * to bf16, fp32 accumulation, fp32 master weights / Adam state / gradient bucket
+ * (SURVEY H5).  Shape class: F + 2 <= 32, H % 128 == 0, batch % 128 == 0
+ * (b200ds_tc_supported); anything else belongs to the fp32 entry points above.
+ *
+ * Operand packs (bf16, tiled for 1-D TMA, see csrc/tc_common.cuh):
+ *   xq : [batch, 32]  = x[b,0..F-1], 1, 1, 0...        b200ds_tc_xq_bytes(batch)
+ *   wq : [H, 32]      = W1[n,0..F-1], hi(b1[n]), lo(b1[n]), 0...  followed by the per-slice
+ *        vectors v = w1q^T w2 the forward uses           b200ds_tc_wq_bytes(H)
+ * x is packed once per batch (after generation / H2D), the weights once per optimizer step. */
+B200DS_API int b200ds_tc_supported(int64_t batch, int n_features, int hidden);
+B200DS_API size_t b200ds_tc_xq_bytes(int64_t batch);
+B200DS_API size_t b200ds_tc_wq_bytes(int hidden);
+B200DS_API int b200ds_pack_x_bf16(const float* x_dev, int64_t batch, int n_features, void* xq_dev,
+                                  uintptr_t stream);
+B200DS_API int b200ds_pack_params_bf16(const float* params_dev, int n_features, int hidden, void* wq_dev,
+                                       uintptr_t stream);
+/* model_engine(batch_x) (train.py:107): logits[b] = relu(xq[b,:] . w1q[n,:]) . W2 + b2, the
+ * hidden activation stays in TMEM/registers.  W2 and b2 are read in fp32 from params_dev. */
+B200DS_API int b200ds_mlp_forward_tc(const void* xq_dev, const void* wq_dev, const float* params_dev,
+                                     int64_t batch, int n_features, int hidden, float* logits_dev,
+                                     uintptr_t stream);
+/* model_engine.backward(loss) up to the all-reduce (train.py:113): recomputes the
+ * activation mask on the tensor cores, accumulates S[n,k] = sum_b 1[z1[b,n]>0] dz[b] xq[b,k]
+ * in TMEM, then dW1 = W2[n] S[n,:F], db1 = W2[n] S[n,F], dW2[n] = sum_k w1q[n,k] S[n,k],
+ * db2 = sum_b dz[b]; grads_dev (flat layout) is overwritten.  dlogits 16-byte aligned. */
+B200DS_API size_t b200ds_mlp_backward_tc_scratch_bytes(int64_t batch, int n_features, int hidden);
+B200DS_API int b200ds_mlp_backward_tc(const void* xq_dev, const void* wq_dev, const float* params_dev,
+                                      const float* dlogits_dev, int64_t batch, int n_features, int hidden,
+                                      float* grads_dev, void* scratch_dev, size_t scratch_bytes,
+                                      uintptr_t stream);
+
 /* ---- end-to-end step with HOST buffers (what bench.py's `e2e` times) ---------------
  * One call = train.py:104-115 for one batch: H2D of x,y from (pinned) host memory,
  * forward, loss, backward, all-reduce, Adam (t = step0 + 1), D2H of the loss, and a

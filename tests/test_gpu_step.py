@@ -152,7 +152,8 @@ def test_loss_extreme_logits(lib, cuda_dev):
     want = float(ora.bce_with_logits(z.reshape(-1, 1), y.reshape(-1, 1)))
     loss = torch.zeros(1, dtype=torch.float32, device=cuda_dev)
     dz = torch.empty(8, dtype=torch.float32, device=cuda_dev)
-    _check(lib, lib.b200ds_bce_loss_grad(z.to(cuda_dev).data_ptr(), y.to(cuda_dev).data_ptr(), 8, loss.data_ptr(),
+    zd, yd = z.to(cuda_dev), y.to(cuda_dev)
+    _check(lib, lib.b200ds_bce_loss_grad(zd.data_ptr(), yd.data_ptr(), 8, loss.data_ptr(),
                                          dz.data_ptr(), None, None, 0, _st()))
     torch.cuda.synchronize()
     assert torch.isfinite(dz).all() and abs(float(loss) - want) <= RTOL * abs(want)
@@ -201,6 +202,8 @@ def test_fused_epoch_matches_reference_world1(lib, cuda_dev, golden):
     x = torch.from_numpy(golden["x"]).to(cuda_dev)
     y = torch.from_numpy(golden["y"]).reshape(-1).to(cuda_dev)
     params, grads, m, v, P, Ppad = _tiny_state(golden, cuda_dev)
+    if str(golden["cpu_capability"][0]) != torch.backends.cpu.get_cpu_capability():
+        pytest.skip("host CPU RNG path differs from the golden host: sample order not reproducible here")
     # the order the reference's DataLoader(shuffle=True) produced: redo its RNG draws
     torch.manual_seed(42)
     ora.make_dataset(2000, 20, 42)
@@ -217,8 +220,6 @@ def test_fused_epoch_matches_reference_world1(lib, cuda_dev, golden):
         losses_all.append(losses.cpu().double().numpy())
     got = np.concatenate(losses_all)
     want = golden["w1_step_losses"][0]
-    if str(golden["cpu_capability"][0]) != torch.backends.cpu.get_cpu_capability():
-        pytest.skip("host CPU RNG path differs from the golden host: sample order not reproducible here")
     assert np.abs(got - want).max() <= RTOL * np.abs(want).max()
     means = [f"{got[e * 500:(e + 1) * 500].sum() / 500:.4f}" for e in range(5)]
     assert means == [f"{v:.4f}" for v in golden["w1_epoch_means"][0]]       # the logged line, to 4 decimals
@@ -249,8 +250,9 @@ def test_fused_steps_vs_oracle_shapes(lib, cuda_dev, B, F, H, steps):
     grads, m, v = zz(), zz(), zz()
     losses = torch.zeros(steps, dtype=torch.float32, device=cuda_dev)
     od = order.to(torch.int64).to(cuda_dev)
+    xd, yd = x.to(cuda_dev), y.reshape(-1).to(cuda_dev)
     _check(lib, lib.b200ds_tiny_train_steps_f32(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), F, H,
-                                                x.to(cuda_dev).data_ptr(), y.reshape(-1).to(cuda_dev).data_ptr(),
+                                                xd.data_ptr(), yd.data_ptr(),
                                                 od.data_ptr(), od.numel(), 0, B, steps, 1, 1e-2, 0.9, 0.999, 1e-8, 0,
                                                 losses.data_ptr(), _st()))
     torch.cuda.synchronize()

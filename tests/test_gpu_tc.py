@@ -1,0 +1,120 @@
+"""Parity of the bf16 tensor-core path (tcgen05/TMEM/TMA kernels) through the C ABI.
+
+Checker: the oracle's bf16 restatement (oracle/reference_step._bf16_step semantics: GEMM
+operands rounded to bf16, fp32 accumulation) evaluated in fp64 by torch on the GPU for the
+big shapes.  Tolerances: logits 1e-4 relative (same bf16 operands, only the summation order
+and the hi/lo bias split differ); gradients 2e-2 (north_star's bf16 tolerance; dz is rounded
+to bf16 once on its way into the tensor core)."""
+import ctypes as C
+
+import pytest
+import torch
+
+from oracle import reference_step as ora
+
+pytestmark = pytest.mark.gpu
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _chk(rc):
+    from b200ds import _lib
+    _lib.check(rc)
+
+
+def _bf(t):
+    return t.to(torch.bfloat16).to(torch.float64)
+
+
+def _reference(p, x, y):
+    """fp64 evaluation of the bf16-operand step (oracle._bf16_step, written for any device)."""
+    xq, w1q = _bf(x), _bf(p["w1"])
+    z1 = xq @ w1q.t() + p["b1"].double()
+    h = torch.clamp_min(z1, 0)
+    z = h @ p["w2"].double().t() + p["b2"].double()
+    B = x.shape[0]
+    dz = (torch.sigmoid(z) - y.double()) / B
+    g_w2 = dz.t() @ h
+    g_b2 = dz.sum(dim=0)
+    dz1 = (dz @ p["w2"].double()) * (h > 0).double()
+    g_w1 = dz1.t() @ xq
+    g_b1 = dz1.sum(dim=0)
+    return z.reshape(-1), dz.reshape(-1), torch.cat([g_w1.reshape(-1), g_b1.reshape(-1), g_w2.reshape(-1), g_b2.reshape(-1)])
+
+
+SHAPES = [(128, 20, 128), (256, 20, 256), (1024, 20, 384), (4096, 30, 2048), (2048, 1, 512), (65536, 20, 4096),
+          (8192, 20, 8192), (384, 7, 640)]
+
+
+@pytest.mark.parametrize("B,F,H", SHAPES)
+def test_tc_forward_backward_vs_bf16_oracle(lib, cuda_dev, B, F, H):
+    assert lib.b200ds_tc_supported(B, F, H) == 1
+    torch.manual_seed(B + 31 * F + 7 * H)
+    p = {k: v.to(cuda_dev) for k, v in ora.init_params(F, H).items()}
+    p["b1"] = p["b1"] + 0.05 * torch.randn(H, device=cuda_dev)          # make the bias matter
+    x = torch.randn(B, F, device=cuda_dev)
+    y = (x[:, : max(1, F // 2)].sum(dim=1, keepdim=True) > 0).float()
+    flat = torch.cat([p[k].reshape(-1) for k in ora.PARAM_ORDER])
+    P = flat.numel()
+    Ppad = (P + 3) // 4 * 4
+    params = torch.zeros(Ppad, device=cuda_dev); params[:P] = flat
+    xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=cuda_dev)
+    wq = torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=cuda_dev)
+    logits = torch.full((B,), float("nan"), device=cuda_dev)
+    grads = torch.full((Ppad,), float("nan"), device=cuda_dev)
+    sc = torch.zeros(max(256, lib.b200ds_mlp_backward_tc_scratch_bytes(B, F, H)), dtype=torch.uint8, device=cuda_dev)
+    _chk(lib.b200ds_pack_x_bf16(x.data_ptr(), B, F, xq.data_ptr(), _st()))
+    _chk(lib.b200ds_pack_params_bf16(params.data_ptr(), F, H, wq.data_ptr(), _st()))
+    _chk(lib.b200ds_mlp_forward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), B, F, H, logits.data_ptr(), _st()))
+    torch.cuda.synchronize()
+    z_ref, dz_ref, g_ref = _reference(p, x, y)
+    zerr = float((logits.double() - z_ref).abs().max() / z_ref.abs().max())
+    assert zerr <= 1e-4, zerr
+    dz = dz_ref.float().contiguous()
+    for rep in range(2):       # twice: the second call must not depend on state left by the first
+        grads.fill_(float("nan"))
+        _chk(lib.b200ds_mlp_backward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), dz.data_ptr(), B, F, H,
+                                        grads.data_ptr(), sc.data_ptr(), sc.numel(), _st()))
+        torch.cuda.synchronize()
+        g = grads[:P].double()
+        assert torch.isfinite(g).all()
+        for name, (o, n) in zip(ora.PARAM_ORDER, ((0, H * F), (H * F, H), (H * F + H, H), (H * F + 2 * H, 1))):
+            err = float((g[o:o + n] - g_ref[o:o + n]).abs().max() / max(1e-30, float(g_ref[o:o + n].abs().max())))
+            assert err <= 2e-2, (name, err, rep)
+
+
+def test_tc_rejects_unsupported_shapes(lib, cuda_dev):
+    assert lib.b200ds_tc_supported(100, 20, 128) == 0        # batch not a multiple of 128
+    assert lib.b200ds_tc_supported(128, 31, 128) == 0        # F + 2 > 32
+    assert lib.b200ds_tc_supported(128, 20, 64) == 0         # H not a multiple of 128
+    assert lib.b200ds_mlp_forward_tc(None, None, None, 100, 20, 128, None, _st()) == 1
+    assert lib.b200ds_mlp_backward_tc_scratch_bytes(100, 20, 128) == 0
+
+
+def test_tc_matches_fp32_path_within_bf16_tolerance(lib, cuda_dev):
+    """The two product paths against each other at full size: same loss to 2e-2."""
+    B, F, H = 65536, 20, 4096
+    torch.manual_seed(3)
+    flat = ora.flatten(ora.init_params(F, H)).to(cuda_dev)
+    P = flat.numel(); Ppad = (P + 3) // 4 * 4
+    params = torch.zeros(Ppad, device=cuda_dev); params[:P] = flat
+    x = torch.empty(B * F, device=cuda_dev)
+    _chk(lib.b200ds_philox_normal(x.data_ptr(), B * F, 42, 0, None, _st()))
+    y = torch.empty(B, device=cuda_dev)
+    _chk(lib.b200ds_label_rule(x.data_ptr(), y.data_ptr(), B, F, _st()))
+    xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=cuda_dev)
+    wq = torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=cuda_dev)
+    z32 = torch.empty(B, device=cuda_dev); z16 = torch.empty(B, device=cuda_dev)
+    _chk(lib.b200ds_mlp_forward_f32(params.data_ptr(), x.data_ptr(), B, F, H, z32.data_ptr(), _st()))
+    _chk(lib.b200ds_pack_x_bf16(x.data_ptr(), B, F, xq.data_ptr(), _st()))
+    _chk(lib.b200ds_pack_params_bf16(params.data_ptr(), F, H, wq.data_ptr(), _st()))
+    _chk(lib.b200ds_mlp_forward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), B, F, H, z16.data_ptr(), _st()))
+    l32 = torch.zeros(1, device=cuda_dev); l16 = torch.zeros(1, device=cuda_dev)
+    sc = torch.zeros(lib.b200ds_bce_scratch_bytes(B), dtype=torch.uint8, device=cuda_dev)
+    _chk(lib.b200ds_bce_loss_grad(z32.data_ptr(), y.data_ptr(), B, l32.data_ptr(), None, None, sc.data_ptr(), sc.numel(), _st()))
+    _chk(lib.b200ds_bce_loss_grad(z16.data_ptr(), y.data_ptr(), B, l16.data_ptr(), None, None, sc.data_ptr(), sc.numel(), _st()))
+    torch.cuda.synchronize()
+    assert abs(float(l16) - float(l32)) <= 2e-2 * abs(float(l32))
+    assert float((z16 - z32).abs().max()) <= 2e-2 * float(z32.abs().max())
