@@ -191,8 +191,15 @@ class WideStep:
         self.counter = torch.zeros(1, dtype=torch.int64, device=dev)
         self.seed = SEED + 1000003 * rank           # distinct Philox key per rank
         self.offset = 0
-        self.launches_per_step = 7
-        self.ev = None
+        self.tc = precision == "bf16"
+        if self.tc:
+            assert lib.b200ds_tc_supported(B, F, H), "bf16 tensor-core path does not take this shape"
+            self.xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=dev)
+            self.wq = torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=dev)
+            self.bwd_sc = torch.zeros(max(256, lib.b200ds_mlp_backward_tc_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
+            self.dominant = dict(name="mlp_bwd_tc_kernel", bound="tensor")
+        # philox, label, [pack_x, pack_w1], forward, loss, backward, finish, adam
+        self.launches_per_step = 9 if self.tc else 7
 
     def step(self, st, ev_pair=None):
         lib, chk = self.lib, self._lib.check
@@ -201,13 +208,23 @@ class WideStep:
         chk(lib.b200ds_philox_normal(self.x.data_ptr(), B * F, self.seed, self.offset, C.byref(adv), st))
         self.offset += adv.value
         chk(lib.b200ds_label_rule(self.x.data_ptr(), self.y.data_ptr(), B, F, st))
-        chk(lib.b200ds_mlp_forward_f32(self.params.data_ptr(), self.x.data_ptr(), B, F, H, self.logits.data_ptr(), st))
+        if self.tc:
+            chk(lib.b200ds_pack_x_bf16(self.x.data_ptr(), B, F, self.xq.data_ptr(), st))
+            chk(lib.b200ds_pack_params_bf16(self.params.data_ptr(), F, H, self.wq.data_ptr(), st))
+            chk(lib.b200ds_mlp_forward_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.params.data_ptr(), B, F, H,
+                                          self.logits.data_ptr(), st))
+        else:
+            chk(lib.b200ds_mlp_forward_f32(self.params.data_ptr(), self.x.data_ptr(), B, F, H, self.logits.data_ptr(), st))
         chk(lib.b200ds_bce_loss_grad(self.logits.data_ptr(), self.y.data_ptr(), B, self.loss.data_ptr(), self.dz.data_ptr(),
                                      self.counter.data_ptr(), self.bce_sc.data_ptr(), self.bce_sc.numel(), st))
         if ev_pair:
             ev_pair[0].record()
-        chk(lib.b200ds_mlp_backward_f32(self.params.data_ptr(), self.x.data_ptr(), self.dz.data_ptr(), B, F, H,
-                                        self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
+        if self.tc:
+            chk(lib.b200ds_mlp_backward_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.params.data_ptr(), self.dz.data_ptr(),
+                                           B, F, H, self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
+        else:
+            chk(lib.b200ds_mlp_backward_f32(self.params.data_ptr(), self.x.data_ptr(), self.dz.data_ptr(), B, F, H,
+                                            self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
         if ev_pair:
             ev_pair[1].record()
         chk(lib.b200ds_allreduce_bucket(self.ctx, self.grads.data_ptr(), self.P, st))
@@ -215,7 +232,7 @@ class WideStep:
                                          self.Ppad, LR, 0.9, 0.999, 1e-8, self.counter.data_ptr(),
                                          1.0 / self.world, 0, st))
 
-    dominant = dict(name="mlp_backward_f32_kernel (+finish)", bound="tensor")
+    dominant = dict(name="mlp_backward_f32_kernel (+finish)", bound="tensor")   # overridden per instance for bf16
 
     def dominant_flops(self):
         # algorithmic work of the backward: dW1 2FH, dh 2H, dW2 2H per sample (recompute not counted)
@@ -235,7 +252,9 @@ def run_ours(a):
     if world > 1:
         comm.init_distributed()
     wl = WORKLOADS[a.workload]
-    precision = "fp32" if a.precision == "auto" else a.precision
+    precision = a.precision
+    if precision == "auto":
+        precision = "bf16" if (a.workload != "tiny" and lib.b200ds_tc_supported(wl["B"], wl["F"], wl["H"])) else "fp32"
     ctx = C.c_void_p()
     nid = comm.exchange_nccl_id(lambda: _nccl_id(lib), le)
     idbuf = C.create_string_buffer(nid, 128) if nid else None
@@ -289,7 +308,7 @@ def run_ours(a):
                     traffic=None, kernel=ws.dominant["name"], kernel_ms=k_ms, peak_source=f"{pk['src']} bf16 sustained",
                     step_frac=step_flops(**wl) / (ms_per_step / 1e3) / 1e12 / pk["tf_sus"])
         # ---- e2e: the C-ABI host-buffer call, H2D/D2H inside the timed region
-        e2e = bench_e2e(lib, ctx, dev, wl, world, a, barrier)
+        e2e = bench_e2e(lib, ctx, dev, wl, world, a, barrier, precision)
         out.update(dict(value=value, ms_per_step=ms_per_step, roofline=roof, e2e=e2e, clocks=clk.summary(),
                         gpu_launches=K * ws.launches_per_step, wall_s=wall, loss_last=loss_last,
                         config={"workload": f"{a.workload}: train.py step, F={wl['F']} H={wl['H']}, {wl['B']} samples/GPU/step "
@@ -333,7 +352,7 @@ def _nccl_id(lib):
     return buf.raw
 
 
-def bench_e2e(lib, ctx, dev, wl, world, a, barrier):
+def bench_e2e(lib, ctx, dev, wl, world, a, barrier, precision):
     """Same step through b200ds_train_step_host: inputs in pinned host memory, loss read
     back to the host every step."""
     import torch.distributed as dist
@@ -347,8 +366,12 @@ def bench_e2e(lib, ctx, dev, wl, world, a, barrier):
     params = z(Ppad); params[:P] = flat.to(dev)
     grads, m, v, xs, ys, lg, dl, ls = z(Ppad), z(Ppad), z(Ppad), z(B * F), z(B), z(B), z(B), z(1)
     sc = torch.zeros(max(256, lib.b200ds_train_step_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
+    tc = precision == "bf16"
+    xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=dev) if tc else None
+    wq = torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=dev) if tc else None
     bufs = _lib.StepBufs(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), xs.data_ptr(), ys.data_ptr(),
-                         lg.data_ptr(), dl.data_ptr(), ls.data_ptr(), sc.data_ptr(), sc.numel())
+                         lg.data_ptr(), dl.data_ptr(), ls.data_ptr(), sc.data_ptr(), sc.numel(),
+                         xq.data_ptr() if tc else None, wq.data_ptr() if tc else None)
     nbuf = 4
     xh = [torch.randn(B, F).pin_memory() for _ in range(nbuf)]
     yh = [label_rule(x).contiguous().pin_memory() for x in xh]

@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200ds.so")
+LIB_PATH = os.environ.get("B200DS_LIB") or os.path.join(_HERE, "libb200ds.so")   # override: tuning builds only
 
 NCCL_ID_BYTES = 128
 
@@ -26,6 +26,7 @@ class StepBufs(C.Structure):
         ("logits", c_ptr), ("dlogits", c_ptr),
         ("loss", c_ptr),
         ("scratch", c_ptr), ("scratch_bytes", C.c_size_t),
+        ("xq", c_ptr), ("wq", c_ptr),
     ]
 
 

@@ -110,6 +110,10 @@ class B200Engine:
         self._x = None
         self._logits = None
         self._scratch = None
+        self._tc = False
+        self._xq = None
+        self._wq = None
+        self._wq_step = -1
         self._bce_scratch = torch.zeros(self.lib.b200ds_bce_scratch_bytes(0), dtype=torch.uint8, device=dev)
 
     # ------------------------------------------------------------------ helpers
@@ -148,8 +152,23 @@ class B200Engine:
         x = x.contiguous()
         B = x.shape[0]
         logits = torch.empty((B, 1), dtype=torch.float32, device=self.device)
-        _lib.check(self.lib.b200ds_mlp_forward_f32(self.flat.data_ptr(), x.data_ptr(), B, self.F, self.H,
-                                                   logits.data_ptr(), _lib.current_stream()), "mlp_forward_f32")
+        stream = _lib.current_stream()
+        self._tc = self.cfg["precision"] == "bf16" and bool(self.lib.b200ds_tc_supported(B, self.F, self.H))
+        if self._tc:
+            # bf16 extension (BASELINE config 3/4): tcgen05 kernels on packed bf16 operands
+            self._xq = torch.empty(self.lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=self.device)
+            if self._wq is None:
+                self._wq = torch.empty(self.lib.b200ds_tc_wq_bytes(self.H), dtype=torch.uint8, device=self.device)
+            _lib.check(self.lib.b200ds_pack_x_bf16(x.data_ptr(), B, self.F, self._xq.data_ptr(), stream), "pack_x_bf16")
+            if self._wq_step != self.global_steps:
+                _lib.check(self.lib.b200ds_pack_params_bf16(self.flat.data_ptr(), self.F, self.H, self._wq.data_ptr(), stream),
+                           "pack_params_bf16")
+                self._wq_step = self.global_steps
+            _lib.check(self.lib.b200ds_mlp_forward_tc(self._xq.data_ptr(), self._wq.data_ptr(), self.flat.data_ptr(), B,
+                                                      self.F, self.H, logits.data_ptr(), stream), "mlp_forward_tc")
+        else:
+            _lib.check(self.lib.b200ds_mlp_forward_f32(self.flat.data_ptr(), x.data_ptr(), B, self.F, self.H,
+                                                       logits.data_ptr(), stream), "mlp_forward_f32")
         self._x = x
         self._logits = logits
         logits._b200ds_engine = weakref.ref(self)
@@ -168,12 +187,17 @@ class B200Engine:
             (dlogits,) = torch.autograd.grad(loss, self._logits)
             dlogits = dlogits.contiguous()
         B = self._x.shape[0]
-        need = self.lib.b200ds_mlp_backward_f32_scratch_bytes(B, self.F, self.H)
-        scratch = self._scratch_for(need)
         stream = _lib.current_stream()
-        _lib.check(self.lib.b200ds_mlp_backward_f32(self.flat.data_ptr(), self._x.data_ptr(), dlogits.data_ptr(), B,
-                                                    self.F, self.H, self.grads.data_ptr(), scratch.data_ptr(),
-                                                    scratch.numel(), stream), "mlp_backward_f32")
+        if self._tc:
+            scratch = self._scratch_for(self.lib.b200ds_mlp_backward_tc_scratch_bytes(B, self.F, self.H))
+            _lib.check(self.lib.b200ds_mlp_backward_tc(self._xq.data_ptr(), self._wq.data_ptr(), self.flat.data_ptr(),
+                                                       dlogits.data_ptr(), B, self.F, self.H, self.grads.data_ptr(),
+                                                       scratch.data_ptr(), scratch.numel(), stream), "mlp_backward_tc")
+        else:
+            scratch = self._scratch_for(self.lib.b200ds_mlp_backward_f32_scratch_bytes(B, self.F, self.H))
+            _lib.check(self.lib.b200ds_mlp_backward_f32(self.flat.data_ptr(), self._x.data_ptr(), dlogits.data_ptr(), B,
+                                                        self.F, self.H, self.grads.data_ptr(), scratch.data_ptr(),
+                                                        scratch.numel(), stream), "mlp_backward_f32")
         # DeepSpeed stage 0: gradients are averaged across ranks before backward() returns
         _lib.check(self.lib.b200ds_allreduce_bucket(self.ctx, self.grads.data_ptr(), self.P, stream), "allreduce_bucket")
 
@@ -245,10 +269,15 @@ class B200Engine:
             "loss": torch.zeros(1, dtype=torch.float32, device=dev),
             "scratch": torch.zeros(max(nbytes, 256), dtype=torch.uint8, device=dev),
         }
+        use_tc = self.cfg["precision"] == "bf16" and self.lib.b200ds_tc_supported(batch, self.F, self.H)
+        if use_tc:
+            keep["xq"] = torch.empty(self.lib.b200ds_tc_xq_bytes(batch), dtype=torch.uint8, device=dev)
+            keep["wq"] = torch.empty(self.lib.b200ds_tc_wq_bytes(self.H), dtype=torch.uint8, device=dev)
         bufs = _lib.StepBufs(self.flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
                              self.exp_avg_sq.data_ptr(), keep["x"].data_ptr(), keep["y"].data_ptr(),
                              keep["z"].data_ptr(), keep["dz"].data_ptr(), keep["loss"].data_ptr(),
-                             keep["scratch"].data_ptr(), keep["scratch"].numel())
+                             keep["scratch"].data_ptr(), keep["scratch"].numel(),
+                             keep["xq"].data_ptr() if use_tc else None, keep["wq"].data_ptr() if use_tc else None)
 
         def host_step(x_host: torch.Tensor, y_host: torch.Tensor, loss_host: torch.Tensor, _keep=keep):
             lr, b1, b2, eps = self._hyper()

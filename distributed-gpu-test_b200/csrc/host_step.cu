@@ -12,8 +12,9 @@ static bool tiny_class(int64_t batch, int F, int H) { return F <= 32 && H <= 256
 extern "C" {
 
 size_t b200ds_train_step_scratch_bytes(int64_t batch, int n_features, int hidden) {
-  return align_up(b200ds_bce_scratch_bytes(batch), 256) +
-         align_up(b200ds_mlp_backward_f32_scratch_bytes(batch, n_features, hidden), 256);
+  size_t f32 = b200ds_mlp_backward_f32_scratch_bytes(batch, n_features, hidden);
+  size_t tcb = b200ds_mlp_backward_tc_scratch_bytes(batch, n_features, hidden);
+  return align_up(b200ds_bce_scratch_bytes(batch), 256) + align_up(f32 > tcb ? f32 : tcb, 256);
 }
 
 int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* b,
@@ -49,10 +50,22 @@ int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* b,
     B200_REQUIRE(b->scratch && b->scratch_bytes >= need, "train_step_host: scratch too small (%zu < %zu)", b->scratch_bytes, need);
     char* sc = reinterpret_cast<char*>(b->scratch);
     size_t bce_bytes = align_up(b200ds_bce_scratch_bytes(batch), 256);
-    if ((rc = b200ds_mlp_forward_f32(b->params, b->x_stage, batch, n_features, hidden, b->logits, stream))) return rc;
+    const bool use_tc = b->xq && b->wq && b200ds_tc_supported(batch, n_features, hidden);
+    if (use_tc) {
+      if ((rc = b200ds_pack_x_bf16(b->x_stage, batch, n_features, b->xq, stream))) return rc;
+      if ((rc = b200ds_pack_params_bf16(b->params, n_features, hidden, b->wq, stream))) return rc;
+      if ((rc = b200ds_mlp_forward_tc(b->xq, b->wq, b->params, batch, n_features, hidden, b->logits, stream))) return rc;
+    } else {
+      if ((rc = b200ds_mlp_forward_f32(b->params, b->x_stage, batch, n_features, hidden, b->logits, stream))) return rc;
+    }
     if ((rc = b200ds_bce_loss_grad(b->logits, b->y_stage, batch, b->loss, b->dlogits, nullptr, sc, bce_bytes, stream))) return rc;
-    if ((rc = b200ds_mlp_backward_f32(b->params, b->x_stage, b->dlogits, batch, n_features, hidden, b->grads,
-                                      sc + bce_bytes, b->scratch_bytes - bce_bytes, stream))) return rc;
+    if (use_tc) {
+      if ((rc = b200ds_mlp_backward_tc(b->xq, b->wq, b->params, b->dlogits, batch, n_features, hidden, b->grads,
+                                       sc + bce_bytes, b->scratch_bytes - bce_bytes, stream))) return rc;
+    } else {
+      if ((rc = b200ds_mlp_backward_f32(b->params, b->x_stage, b->dlogits, batch, n_features, hidden, b->grads,
+                                        sc + bce_bytes, b->scratch_bytes - bce_bytes, stream))) return rc;
+    }
     if ((rc = b200ds_allreduce_bucket(ctx, b->grads, P, stream))) return rc;
     if ((rc = b200ds_adam_step(b->params, b->grads, b->exp_avg, b->exp_avg_sq, Ppad, lr, beta1, beta2, eps,
                                step0 + 1, scale, 0, stream))) return rc;

@@ -58,56 +58,68 @@ pack_x_kernel(const float* __restrict__ x, int64_t batch, int F, uint4* __restri
   xq[t] = *reinterpret_cast<uint4*>(v);
 }
 
+constexpr int kPackRows = 64;             // rows of W1 per pack_w1 block (256 threads = 64 rows x 4 k chunks)
+
+// Also emits, per block of 64 rows, vpart[block][k] = sum_{n in block} w2[n] * w1q[n,k]: the forward
+// sums the blocks of its slice in a fixed order to get v = w1q^T w2 (the linear half of relu).
 __global__ void __launch_bounds__(256)
-pack_w1_kernel(const float* __restrict__ params, Layout L, uint4* __restrict__ w1q) {
-  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= (int64_t)L.H * (KP / 8)) return;
-  int r8 = (int)(t & 7), c = (int)((t >> 3) & 3);
-  int n = (int)(((t >> 5) << 3) + r8);
+pack_w1_kernel(const float* __restrict__ params, Layout L, uint4* __restrict__ w1q, float* __restrict__ vpart) {
+  __shared__ float prod[kPackRows][33];
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;     // H % 64 == 0: no partial blocks
+  const int r8 = (int)(t & 7), c = (int)((t >> 3) & 3);
+  const int n = (int)(((t >> 5) << 3) + r8);
   const float* wr = params + L.off_w1() + (int64_t)n * L.F;
-  float b1 = params[L.off_b1() + n];
-  __nv_bfloat16 hi = __float2bfloat16(b1);
-  __nv_bfloat16 lo = __float2bfloat16(b1 - __bfloat162float(hi));
+  const float b1 = params[L.off_b1() + n];
+  const float w2 = params[L.off_w2() + n];
+  const __nv_bfloat16 hi = __float2bfloat16(b1);
+  const __nv_bfloat16 lo = __float2bfloat16(b1 - __bfloat162float(hi));
   __nv_bfloat16 v[8];
+  const int rl = n - blockIdx.x * kPackRows;
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     int k = c * 8 + j;
     v[j] = k < L.F ? __float2bfloat16(wr[k]) : (k == L.F ? hi : (k == L.F + 1 ? lo : __float2bfloat16(0.f)));
+    prod[rl][k] = w2 * __bfloat162float(v[j]);
   }
   w1q[t] = *reinterpret_cast<uint4*>(v);
-}
-
-// v[s][k] = sum_{n in slice s} w2[n] * w1q[n,k]   (deterministic order), one CTA per slice
-__global__ void __launch_bounds__(1024)
-lin_vector_kernel(const float* __restrict__ params, Layout L, const unsigned char* __restrict__ w1q, int slice_rows,
-                  float* __restrict__ v) {
-  __shared__ float part[32][33];
-  const int k = threadIdx.x & 31, j = threadIdx.x >> 5;
-  const int n0 = blockIdx.x * slice_rows;
-  const float* w2 = params + L.off_w2();
-  float a = 0.f;
-  for (int n = n0 + j; n < n0 + slice_rows; n += 32)
-    a = fmaf(w2[n], __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(w1q + tiled_byte(n, k))), a);
-  part[j][k] = a;
   __syncthreads();
-  if (j == 0) {
-    float s = 0.f;
-    for (int i = 0; i < 32; ++i) s += part[i][k];
-    v[blockIdx.x * 32 + k] = s;
+  if (threadIdx.x < 32) {
+    float a = 0.f;
+    for (int r = 0; r < kPackRows; ++r) a += prod[r][threadIdx.x];
+    vpart[(size_t)blockIdx.x * 32 + threadIdx.x] = a;
   }
 }
 
 // ------------------------------------------------------------------ forward
+// D1T[n, b] = w1_chunk . x_tile^T puts the hidden unit n on the TMEM lane, so the layer-2 weight
+// w2[n] is ONE register per thread per chunk (no shared-memory broadcast traffic next to the
+// UMMA operand reads, which already use the full 128 B/clk), and each thread keeps 64 running
+// sums acc[b] += w2[n] |z1[n,b]| across all chunks of the tile.  The sum over n (lanes, then
+// the 4 lane quadrants) happens once per tile.
 constexpr int kFwdXStages = 3;
-constexpr int kFwdRing = 4;               // D1 accumulators in TMEM: 4 x 128 columns
-constexpr int kFwdThreads = 32 * 10;      // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue (two groups)
+constexpr int kFwdRing = 4;               // D1T accumulators in TMEM: 4 x 128 columns
+constexpr int kFwdEpiWarps = 8;           // warp (quad, half): 32 lanes (n) x 64 columns (b)
+constexpr int kFwdThreads = 32 * 11;      // warp 0 TMA, warp 1 / warp 10 MMA (even / odd chunks), warps 2-9 epilogue
 
 struct FwdSmem {                           // fixed-size tail after the W1 slice / w2 slice / x stages
   float v[32];
-  float zs[2][128];
+  float red[2][4][64];                     // [column half][lane quadrant][column]: per-warp column sums
   uint64_t w_bar, x_full[kFwdXStages], x_free[kFwdXStages], d1_full[kFwdRing], d1_free[kFwdRing];
   uint32_t tmem_slot;
 };
+
+// sum over the 32 lanes of 64 per-lane values; lane l ends with the totals of columns
+// col(l), col(l)+1 where col(l) = 2 * bitreverse5(l)... precisely: bit4->+32, bit3->+16, bit2->+8, bit1->+4, bit0->+2
+template <int N, int OFF>
+__device__ __forceinline__ void lane_fold(float (&a)[64], int lane) {
+  const bool up = (lane & OFF) != 0;
+#pragma unroll
+  for (int i = 0; i < N / 2; ++i) {
+    const float keep = up ? a[i + N / 2] : a[i];
+    const float send = up ? a[i] : a[i + N / 2];
+    a[i] = keep + __shfl_xor_sync(0xffffffffu, send, OFF);
+  }
+}
 
 __global__ void __launch_bounds__(kFwdThreads, 1)
 mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __restrict__ w1q,
@@ -121,16 +133,23 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
   float* w2s = reinterpret_cast<float*>(w1s + (size_t)slice_rows * KP * 2);       // [slice_rows] fp32
   unsigned char* xs = reinterpret_cast<unsigned char*>(w2s + slice_rows);         // [stages][8192]
   FwdSmem* sh = reinterpret_cast<FwdSmem*>(xs + kFwdXStages * kTileBytes);
+  const uint32_t n_issuers = NC < 2 ? 1u : 2u;
 
   if (threadIdx.x == 0) {
     mbar_init(&sh->w_bar, 1);
-    for (int i = 0; i < kFwdXStages; ++i) { mbar_init(&sh->x_full[i], 1); mbar_init(&sh->x_free[i], 1); }
-    for (int i = 0; i < kFwdRing; ++i) { mbar_init(&sh->d1_full[i], 1); mbar_init(&sh->d1_free[i], 4); }
+    for (int i = 0; i < kFwdXStages; ++i) { mbar_init(&sh->x_full[i], 1); mbar_init(&sh->x_free[i], n_issuers); }
+    for (int i = 0; i < kFwdRing; ++i) { mbar_init(&sh->d1_full[i], 1); mbar_init(&sh->d1_free[i], kFwdEpiWarps); }
     mbar_fence_init();
   }
   if (warp == 1) tmem_alloc<512>(&sh->tmem_slot);
   for (int i = threadIdx.x; i < slice_rows; i += blockDim.x) w2s[i] = w2[slice * slice_rows + i];
-  if (threadIdx.x < 32) sh->v[threadIdx.x] = vlin[slice * 32 + threadIdx.x];
+  if (threadIdx.x < 32) {      // v = sum over the 64-row blocks of this slice, fixed order
+    const int nblk = slice_rows / kPackRows;
+    const float* vp = vlin + (size_t)slice * nblk * 32 + threadIdx.x;
+    float a = 0.f;
+    for (int i = 0; i < nblk; ++i) a += vp[(size_t)i * 32];
+    sh->v[threadIdx.x] = a;
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -150,40 +169,54 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         if (++s == kFwdXStages) { s = 0; ph ^= 1; }
       }
     }
-  } else if (warp == 1) {
-    // ===== MMA issuer: D1[ring] = x_tile . w1_chunk^T, K = 32 =====
-    if (lane == 0) {
+  } else if (warp == 1 || warp == 10) {
+    // ===== MMA issuers (chunk parity): D1T[ring] = w1_chunk . x_tile^T, K = 32.  The whole warp
+    // walks the loop (uniform control flow); one elected lane issues.  Two issuing warps because
+    // one warp's wait + issue + commit round is longer than the 132 cycles a chunk executes. =====
+    const int me = warp == 1 ? 0 : 1;
+    if (me < NC) {
       const uint32_t idesc = idesc_bf16(128, 128, 0, 0);
       const uint64_t xdesc0 = smem_desc(smem_u32(xs), LBO_K, SBO_K);
       const uint64_t wdesc0 = smem_desc(smem_u32(w1s), LBO_K, SBO_K);
       mbar_wait(&sh->w_bar, 0);
-      int s = 0; uint32_t xph = 0; int r = 0; uint32_t rph = 0;
+      int s = 0; uint32_t xph = 0; int q = 0;
       for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice) {
         mbar_wait(&sh->x_full[s], xph);
         const uint64_t xd = xdesc0 + (uint64_t)((s * kTileBytes) >> 4);
-        for (int c = 0; c < NC; ++c) {
-          mbar_wait(&sh->d1_free[r], rph ^ 1);
-          tc_fence_after();
+        for (int c = 0; c < NC; ++c, ++q) {
+          if ((c & 1) != me) continue;
+          const int r = q % kFwdRing;
+          const uint32_t rph = (uint32_t)(q / kFwdRing) & 1u;
           const uint64_t wd = wdesc0 + (uint64_t)((c * kTileBytes) >> 4);
-          mma_ss(tmem + r * 128, xd, wd, idesc, 0);
-          mma_ss(tmem + r * 128, xd + (2 * LBO_K >> 4), wd + (2 * LBO_K >> 4), idesc, 1);
-          mma_commit(&sh->d1_full[r]);
-          if (++r == kFwdRing) { r = 0; rph ^= 1; }
+          const uint32_t dcol = tmem + r * 128;
+#if !defined(B200DS_ABLATE) || B200DS_ABLATE < 3
+          mbar_wait(&sh->d1_free[r], rph ^ 1);
+#endif
+          tc_fence_after();
+          if (elect_one()) {
+            mma_ss(dcol, wd, xd, idesc, 0);
+            mma_ss(dcol, wd + (2 * LBO_K >> 4), xd + (2 * LBO_K >> 4), idesc, 1);
+#if !defined(B200DS_ABLATE) || B200DS_ABLATE < 4
+            mma_commit(&sh->d1_full[r]);
+#endif
+          }
+          __syncwarp();
         }
-        mma_commit(&sh->x_free[s]);
+        if (elect_one()) mma_commit(&sh->x_free[s]);
+        __syncwarp();
         if (++s == kFwdXStages) { s = 0; xph ^= 1; }
       }
     }
   } else {
-    // ===== epilogue: two groups of 4 warps; group g takes the chunks with c % 2 == g =====
-    const int ew = warp - 2, grp = ew >> 2, quad = warp & 3;
-    const int row = quad * 32 + lane;
+    // ===== epilogue: 8 warps on every chunk =====
+    const int half = (warp - 2) >> 2, quad = warp & 3;
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const int row = quad * 32 + lane;                      // the b row this thread finishes (half 0 warps only)
     const float b2 = slice == 0 ? b2p[0] : 0.f;
-    int s = 0; uint32_t xph = 0; int q = 0; int tcount = 0;
-    for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice, ++tcount) {
+    int s = 0; uint32_t xph = 0; int q = 0;
+    for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice) {
       float lin = 0.f;
-      if (grp == 0) {       // linear half of relu: xq[row,:] . v, from the x tile in smem
+      if (half == 0) {       // linear half of relu: xq[row,:] . v, from the x tile in smem
         mbar_wait(&sh->x_full[s], xph);
         const unsigned char* xr = xs + s * kTileBytes + (size_t)(row >> 3) * SBO_K + (size_t)(row & 7) * 16;
 #pragma unroll
@@ -199,38 +232,54 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         }
       }
       if (++s == kFwdXStages) { s = 0; xph ^= 1; }
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+      float acc[64];
+#pragma unroll
+      for (int i = 0; i < 64; ++i) acc[i] = 0.f;
       for (int c = 0; c < NC; ++c, ++q) {
-        if ((q & 1) != grp) continue;
+#if defined(B200DS_ABLATE) && B200DS_ABLATE >= 3
+        continue;
+#endif
         const int r = q % kFwdRing;
         const uint32_t rph = (uint32_t)(q / kFwdRing) & 1u;
+        const float w2n = w2s[c * kTileRows + quad * 32 + lane];
+        const uint32_t tbase = tmem + lane_base + r * 128 + half * 64;
         mbar_wait(&sh->d1_full[r], rph);
         tc_fence_after();
-        const float* wc = w2s + c * kTileRows;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint32_t v[32];
-          tmem_ld32(tmem + lane_base + r * 128 + j * 32, v);
-          tmem_wait_ld();
-#pragma unroll
-          for (int i = 0; i < 32; i += 4) {
-            float4 w4 = *reinterpret_cast<const float4*>(wc + j * 32 + i);
-            a0 = fmaf(fabsf(__uint_as_float(v[i + 0])), w4.x, a0);
-            a1 = fmaf(fabsf(__uint_as_float(v[i + 1])), w4.y, a1);
-            a2 = fmaf(fabsf(__uint_as_float(v[i + 2])), w4.z, a2);
-            a3 = fmaf(fabsf(__uint_as_float(v[i + 3])), w4.w, a3);
-          }
-        }
+        uint32_t va[32], vb[32];
+#if !defined(B200DS_ABLATE) || B200DS_ABLATE < 2
+        tmem_ld32(tbase, va);
+        tmem_ld32(tbase + 32, vb);
+        tmem_wait_ld();
+#else
+        for (int i = 0; i < 32; ++i) { va[i] = tbase + i; vb[i] = tbase - i; }
+#endif
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&sh->d1_free[r]);
+        if (lane == 0) mbar_arrive(&sh->d1_free[r]);     // the chunk is in registers: the buffer can be refilled
+#if !defined(B200DS_ABLATE) || B200DS_ABLATE < 1
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[i] = fmaf(fabsf(__uint_as_float(va[i])), w2n, acc[i]);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[32 + i] = fmaf(fabsf(__uint_as_float(vb[i])), w2n, acc[32 + i]);
+#else
+        acc[0] += __uint_as_float(va[0] ^ vb[1]) * w2n;
+#endif
       }
-      const float absum = (a0 + a1) + (a2 + a3);
-      float* zs = sh->zs[tcount & 1];
-      if (grp == 1) zs[row] = absum;
-      asm volatile("bar.sync 1, 256;" ::: "memory");       // the 8 epilogue warps only
-      if (grp == 0) {
-        float z = 0.5f * (lin + (absum + zs[row])) + b2;
+      // ---- sum over n: 32 lanes by a transposing butterfly, then the 4 quadrants through smem
+      lane_fold<64, 16>(acc, lane);
+      lane_fold<32, 8>(acc, lane);
+      lane_fold<16, 4>(acc, lane);
+      lane_fold<8, 2>(acc, lane);
+      lane_fold<4, 1>(acc, lane);
+      const int col = ((lane & 16) ? 32 : 0) + ((lane & 8) ? 16 : 0) + ((lane & 4) ? 8 : 0) + ((lane & 2) ? 4 : 0) + ((lane & 1) ? 2 : 0);
+      asm volatile("bar.sync 1, 256;" ::: "memory");       // previous tile's red[] has been consumed
+      sh->red[half][quad][col] = acc[0];
+      sh->red[half][quad][col + 1] = acc[1];
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (half == 0) {
+        const int hb = row >> 6, cb = row & 63;
+        const float ab = (sh->red[hb][0][cb] + sh->red[hb][1][cb]) + (sh->red[hb][2][cb] + sh->red[hb][3][cb]);
+        const float z = 0.5f * (lin + ab) + b2;
         float* dst = logits + (size_t)t * kTileRows + row;
         if (n_slices == 1) *dst = z;
         else atomicAdd(dst, z);
@@ -246,7 +295,7 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
 constexpr int kBwdXStages = 4;
 constexpr int kBwdRing = 3;               // D1T accumulators: 3 x 128 columns (cols 0..383)
 constexpr int kBwdNB = 4;                 // n blocks per CTA: S accumulators 4 x 32 columns (cols 384..511)
-constexpr int kBwdThreads = 32 * 12;      // 0 TMA, 1 MMA1, 2 MMA2, 3 dz stager, 4-11 epilogue (two groups)
+constexpr int kBwdThreads = 32 * 12;      // 0 TMA + dz stager, 1 MMA1, 2-3 MMA2 (n block parity), 4-11 epilogue (two groups)
 
 struct BwdSmem {
   uint32_t dzs[kBwdXStages][64];          // dz of the tile as bf16x2 pairs
@@ -258,7 +307,7 @@ struct BwdSmem {
 __global__ void __launch_bounds__(kBwdThreads, 1)
 mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __restrict__ w1q,
                   const float* __restrict__ dz, float* __restrict__ partial /* [splits][H][32] */,
-                  int n_btiles, int hidden, int nb, int n_groups, int n_splits) {
+                  float* __restrict__ db2_part /* [splits] */, int n_btiles, int hidden, int nb, int n_groups, int n_splits) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int group = blockIdx.x % n_groups, split = blockIdx.x / n_groups;
@@ -271,9 +320,10 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
 
   if (threadIdx.x == 0) {
     mbar_init(&sh->w_bar, 1);
-    for (int i = 0; i < kBwdXStages; ++i) { mbar_init(&sh->x_full[i], 1); mbar_init(&sh->x_free[i], 1); mbar_init(&sh->dz_full[i], 1); }
+    const uint32_t n_issuers = nb < 2 ? 1u : 2u;     // MMA2 issuing threads that commit per tile
+    for (int i = 0; i < kBwdXStages; ++i) { mbar_init(&sh->x_full[i], 1); mbar_init(&sh->x_free[i], n_issuers); mbar_init(&sh->dz_full[i], 1); }
     for (int i = 0; i < kBwdRing; ++i) { mbar_init(&sh->d1_full[i], 1); mbar_init(&sh->d1_free[i], 1); mbar_init(&sh->a_ready[i], 4); }
-    mbar_init(&sh->s_full, 1);
+    mbar_init(&sh->s_full, n_issuers);
     mbar_fence_init();
   }
   if (warp == 1) tmem_alloc<512>(&sh->tmem_slot);
@@ -284,24 +334,22 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
   const uint32_t s_col0 = kBwdRing * 128;
 
   if (warp == 0) {
+    // ===== TMA producer (lane 0) + dz stager (all lanes): dz[b0..b0+127] -> bf16x2 pairs in smem =====
     if (lane == 0) {
       const unsigned char* wsrc = w1q + (size_t)group * nb * kTileBytes;
       mbar_arrive_expect_tx(&sh->w_bar, (uint32_t)nb * kTileBytes);
       for (int i = 0; i < nb; ++i) tma_load_1d(w1s + (size_t)i * kTileBytes, wsrc + (size_t)i * kTileBytes, kTileBytes, &sh->w_bar);
-      int s = 0; uint32_t ph = 0;
-      for (int t = t_begin; t < t_end; ++t) {
-        mbar_wait(&sh->x_free[s], ph ^ 1);
-        mbar_arrive_expect_tx(&sh->x_full[s], kTileBytes);
-        tma_load_1d(xs + s * kTileBytes, xq + (size_t)t * kTileBytes, kTileBytes, &sh->x_full[s]);
-        if (++s == kBwdXStages) { s = 0; ph ^= 1; }
-      }
     }
-  } else if (warp == 3) {
-    // ===== dz stager: dz[b0..b0+127] -> bf16x2 pairs in smem =====
     int s = 0; uint32_t ph = 0;
+    float dsum = 0.f;
     for (int t = t_begin; t < t_end; ++t) {
       mbar_wait(&sh->x_free[s], ph ^ 1);
+      if (lane == 0) {
+        mbar_arrive_expect_tx(&sh->x_full[s], kTileBytes);
+        tma_load_1d(xs + s * kTileBytes, xq + (size_t)t * kTileBytes, kTileBytes, &sh->x_full[s]);
+      }
       float4 d = *reinterpret_cast<const float4*>(dz + (size_t)t * kTileRows + lane * 4);
+      dsum += (d.x + d.y) + (d.z + d.w);
       __nv_bfloat162 p0 = __floats2bfloat162_rn(d.x, d.y), p1 = __floats2bfloat162_rn(d.z, d.w);
       sh->dzs[s][lane * 2 + 0] = *reinterpret_cast<uint32_t*>(&p0);
       sh->dzs[s][lane * 2 + 1] = *reinterpret_cast<uint32_t*>(&p1);
@@ -309,9 +357,11 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
       if (lane == 0) mbar_arrive(&sh->dz_full[s]);
       if (++s == kBwdXStages) { s = 0; ph ^= 1; }
     }
+    dsum = warp_sum(dsum);       // this split's share of db2 = sum_b dz[b]
+    if (group == 0 && lane == 0) db2_part[split] = dsum;
   } else if (warp == 1) {
     // ===== MMA1 issuer: D1T[ring] = w1_block . x_tile^T (lanes = n, columns = b) =====
-    if (lane == 0) {
+    {
       const uint32_t idesc = idesc_bf16(128, 128, 0, 0);
       const uint64_t xdesc0 = smem_desc(smem_u32(xs), LBO_K, SBO_K);
       const uint64_t wdesc0 = smem_desc(smem_u32(w1s), LBO_K, SBO_K);
@@ -321,39 +371,55 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         mbar_wait(&sh->x_full[s], xph);
         const uint64_t xd = xdesc0 + (uint64_t)((s * kTileBytes) >> 4);
         for (int i = 0; i < nb; ++i) {
+          const uint64_t wd = wdesc0 + (uint64_t)((i * kTileBytes) >> 4);
+          const uint32_t dcol = tmem + r * 128;
           mbar_wait(&sh->d1_free[r], rph ^ 1);
           tc_fence_after();
-          const uint64_t wd = wdesc0 + (uint64_t)((i * kTileBytes) >> 4);
-          mma_ss(tmem + r * 128, wd, xd, idesc, 0);
-          mma_ss(tmem + r * 128, wd + (2 * LBO_K >> 4), xd + (2 * LBO_K >> 4), idesc, 1);
-          mma_commit(&sh->d1_full[r]);
+          if (elect_one()) {
+            mma_ss(dcol, wd, xd, idesc, 0);
+            mma_ss(dcol, wd + (2 * LBO_K >> 4), xd + (2 * LBO_K >> 4), idesc, 1);
+            mma_commit(&sh->d1_full[r]);
+          }
+          __syncwarp();
           if (++r == kBwdRing) { r = 0; rph ^= 1; }
         }
         if (++s == kBwdXStages) { s = 0; xph ^= 1; }
       }
     }
-  } else if (warp == 2) {
-    // ===== MMA2 issuer: S[i] += A2[ring] (TMEM, bf16) . x_tile (MN-major view), K = 128 rows of b =====
-    if (lane == 0) {
+  } else if (warp == 2 || warp == 3) {
+    // ===== MMA2 issuers: S[i] += A2[ring] (TMEM, bf16) . x_tile (MN-major view), K = 128 rows of b.
+    // n block i belongs to issuer i % 2 for the whole kernel, so the accumulation order into
+    // S[i] is that thread's program order; two issuing threads lift the per-thread issue rate.
+    const int me = warp - 2;
+    if (me < nb) {
       const uint32_t idesc = idesc_bf16(128, 32, 0, 1);
       const uint64_t gdesc0 = smem_desc(smem_u32(xs), /*LBO = K groups*/ SBO_K, /*SBO = N groups*/ LBO_K);
-      int s = 0; int r = 0; uint32_t rph = 0;
+      int s = 0; int q = 0;
       for (int t = t_begin; t < t_end; ++t) {
         const uint64_t gd = gdesc0 + (uint64_t)((s * kTileBytes) >> 4);
-        for (int i = 0; i < nb; ++i) {
+        const uint32_t first = t > t_begin ? 1u : 0u;
+        for (int i = 0; i < nb; ++i, ++q) {
+          if ((i & 1) != me) continue;
+          const int r = q % kBwdRing;
+          const uint32_t rph = (uint32_t)(q / kBwdRing) & 1u;
+          const uint32_t scol = tmem + s_col0 + i * 32, acol = tmem + r * 128;
           mbar_wait(&sh->a_ready[r], rph);
           tc_fence_after();
+          if (elect_one()) {
+            mma_ts(scol, acol, gd, idesc, first);
 #pragma unroll
-          for (int u = 0; u < 8; ++u)
-            mma_ts(tmem + s_col0 + i * 32, tmem + r * 128 + u * 8, gd + (uint64_t)((u * 2 * SBO_K) >> 4), idesc,
-                   (t > t_begin || u > 0) ? 1u : 0u);
-          mma_commit(&sh->d1_free[r]);
-          if (++r == kBwdRing) { r = 0; rph ^= 1; }
+            for (int u = 1; u < 8; ++u)
+              mma_ts(scol, acol + u * 8, gd + (uint64_t)((u * 2 * SBO_K) >> 4), idesc, 1u);
+            mma_commit(&sh->d1_free[r]);
+          }
+          __syncwarp();
         }
-        mma_commit(&sh->x_free[s]);
+        if (elect_one()) mma_commit(&sh->x_free[s]);
+        __syncwarp();
         if (++s == kBwdXStages) s = 0;
       }
-      mma_commit(&sh->s_full);
+      if (elect_one()) mma_commit(&sh->s_full);
+      __syncwarp();
     }
   } else {
     // ===== epilogue: mask * dz -> bf16, in place; chunk q goes to group q % 2 =====
@@ -371,27 +437,34 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         mbar_wait(&sh->d1_full[r], rph);
         tc_fence_after();
         const uint4* dzp = reinterpret_cast<const uint4*>(sh->dzs[s]);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint32_t v[32];
-          tmem_ld32(tmem + lane_base + r * 128 + j * 32, v);
-          tmem_wait_ld();
-          uint32_t p[16];
-#pragma unroll
-          for (int c4 = 0; c4 < 4; ++c4) {
-            uint4 d4 = dzp[j * 4 + c4];
-            const uint32_t dd[4] = {d4.x, d4.y, d4.z, d4.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int c = c4 * 4 + e;
-              uint32_t h = pack_relu_bf16x2(__uint_as_float(v[2 * c]), __uint_as_float(v[2 * c + 1]));
-              uint32_t m;
-              asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(m) : "r"(h), "r"(0u));
-              p[c] = m & dd[e];
-            }
-          }
-          tmem_st16(tmem + lane_base + r * 128 + j * 16, p);
+        const uint32_t tbase = tmem + lane_base + r * 128;
+        uint32_t va[32], vb[32];
+        uint4 d4[4];
+        tmem_ld32(tbase, va);
+        // piece j: dz pairs loaded and the next TMEM load issued before this piece is converted
+#define B200_BWD_PIECE(J, CUR, NXT)                                                               \
+        {                                                                                          \
+          _Pragma("unroll") for (int c4 = 0; c4 < 4; ++c4) d4[c4] = dzp[(J) * 4 + c4];            \
+          tmem_wait_ld();                                                                          \
+          if ((J) < 3) tmem_ld32(tbase + ((J) + 1) * 32, NXT);                                     \
+          uint32_t p[16];                                                                          \
+          _Pragma("unroll") for (int c4 = 0; c4 < 4; ++c4) {                                      \
+            const uint32_t dd[4] = {d4[c4].x, d4[c4].y, d4[c4].z, d4[c4].w};                       \
+            _Pragma("unroll") for (int e = 0; e < 4; ++e) {                                       \
+              const int c = c4 * 4 + e;                                                            \
+              uint32_t h = pack_relu_bf16x2(__uint_as_float(CUR[2 * c]), __uint_as_float(CUR[2 * c + 1])); \
+              uint32_t m;                                                                          \
+              asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(m) : "r"(h), "r"(0u));                    \
+              p[c] = m & dd[e];                                                                    \
+            }                                                                                      \
+          }                                                                                        \
+          tmem_st16(tbase + (J) * 16, p);                                                          \
         }
+        B200_BWD_PIECE(0, va, vb)
+        B200_BWD_PIECE(1, vb, va)
+        B200_BWD_PIECE(2, va, vb)
+        B200_BWD_PIECE(3, vb, va)
+#undef B200_BWD_PIECE
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();
@@ -423,15 +496,24 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
   if (warp == 1) tmem_dealloc<512>(tmem);
 }
 
-// grads from S: one warp per hidden unit n, lane = k
+// grads from S: one warp per hidden unit n, lane = k; split partials summed in split order
 __global__ void __launch_bounds__(256)
-mlp_bwd_tc_finish(const float* __restrict__ partial, int n_splits, const float* __restrict__ params,
-                  const float* __restrict__ dz, int64_t batch, Layout L, float* __restrict__ grads) {
+mlp_bwd_tc_finish(const float* __restrict__ partial, const float* __restrict__ db2_part, int n_splits,
+                  const float* __restrict__ params, Layout L, float* __restrict__ grads) {
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
+  const size_t stride = (size_t)L.H * 32;
   for (int n = blockIdx.x * wpb + (threadIdx.x >> 5); n < L.H; n += gridDim.x * wpb) {
+    const float* p = partial + (size_t)n * 32 + lane;
     float s = 0.f;
-    for (int sp = 0; sp < n_splits; ++sp) s += partial[((size_t)sp * L.H + n) * 32 + lane];
+    int sp = 0;
+    for (; sp + 8 <= n_splits; sp += 8) {           // 8 independent loads in flight, summed in order
+      float v0 = p[(size_t)(sp + 0) * stride], v1 = p[(size_t)(sp + 1) * stride], v2 = p[(size_t)(sp + 2) * stride],
+            v3 = p[(size_t)(sp + 3) * stride], v4 = p[(size_t)(sp + 4) * stride], v5 = p[(size_t)(sp + 5) * stride],
+            v6 = p[(size_t)(sp + 6) * stride], v7 = p[(size_t)(sp + 7) * stride];
+      s = ((((((((s + v0) + v1) + v2) + v3) + v4) + v5) + v6) + v7);
+    }
+    for (; sp < n_splits; ++sp) s += p[(size_t)sp * stride];
     const float w2 = params[L.off_w2() + n];
     float wq;
     if (lane < L.F) {
@@ -448,18 +530,10 @@ mlp_bwd_tc_finish(const float* __restrict__ partial, int n_splits, const float* 
     float d2 = warp_sum(wq * s);
     if (lane == 0) grads[L.off_w2() + n] = d2;
   }
-  if (blockIdx.x == 0) {
-    __shared__ float wp[8];
-    float a = 0.f;
-    for (int64_t i = threadIdx.x; i < batch; i += blockDim.x) a += dz[i];
-    a = warp_sum(a);
-    if (lane == 0) wp[threadIdx.x >> 5] = a;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      float t = 0.f;
-      for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += wp[w];
-      grads[L.off_b2()] = t;
-    }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    float t = 0.f;
+    for (int sp = 0; sp < n_splits; ++sp) t += db2_part[sp];
+    grads[L.off_b2()] = t;
   }
 }
 
@@ -514,7 +588,7 @@ int b200ds_tc_supported(int64_t batch, int n_features, int hidden) {
 
 size_t b200ds_tc_xq_bytes(int64_t batch) { return batch > 0 ? (size_t)batch * KP * 2 : 0; }
 
-size_t b200ds_tc_wq_bytes(int hidden) { return hidden > 0 ? (size_t)hidden * KP * 2 + kMaxSlices * 32 * sizeof(float) : 0; }
+size_t b200ds_tc_wq_bytes(int hidden) { return hidden > 0 ? (size_t)hidden * KP * 2 + (size_t)(hidden / kPackRows) * 32 * sizeof(float) : 0; }
 
 int b200ds_pack_x_bf16(const float* x_dev, int64_t batch, int n_features, void* xq_dev, uintptr_t stream) {
   B200_REQUIRE(batch > 0 && batch % 8 == 0, "pack_x_bf16: batch must be a positive multiple of 8 (got %lld)", (long long)batch);
@@ -533,12 +607,9 @@ int b200ds_pack_params_bf16(const float* params_dev, int n_features, int hidden,
   FwdPlan fp;
   B200_REQUIRE(fwd_plan(128, hidden, &fp), "pack_params_bf16: H = %d cannot be sliced into <= %d resident slices", hidden, kMaxSlices);
   Layout L{n_features, hidden};
-  int64_t threads = (int64_t)hidden * (KP / 8);
-  pack_w1_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, as_stream(stream)>>>(params_dev, L, reinterpret_cast<uint4*>(wq_dev));
-  B200_LAUNCH_CHECK();
   unsigned char* w1q = reinterpret_cast<unsigned char*>(wq_dev);
-  float* v = reinterpret_cast<float*>(w1q + (size_t)hidden * KP * 2);
-  lin_vector_kernel<<<fp.slices, 1024, 0, as_stream(stream)>>>(params_dev, L, w1q, fp.slice_rows, v);
+  float* vpart = reinterpret_cast<float*>(w1q + (size_t)hidden * KP * 2);
+  pack_w1_kernel<<<hidden / kPackRows, 256, 0, as_stream(stream)>>>(params_dev, L, reinterpret_cast<uint4*>(wq_dev), vpart);
   B200_LAUNCH_CHECK();
   return B200DS_OK;
 }
@@ -574,7 +645,7 @@ size_t b200ds_mlp_backward_tc_scratch_bytes(int64_t batch, int n_features, int h
   if (!tc_shape_ok(batch, n_features, hidden)) return 0;
   BwdPlan bp;
   bwd_plan(batch, hidden, &bp);
-  return (size_t)bp.splits * hidden * 32 * sizeof(float);
+  return (size_t)bp.splits * hidden * 32 * sizeof(float) + (size_t)bp.splits * sizeof(float);
 }
 
 int b200ds_mlp_backward_tc(const void* xq_dev, const void* wq_dev, const float* params_dev,
@@ -587,7 +658,7 @@ int b200ds_mlp_backward_tc(const void* xq_dev, const void* wq_dev, const float* 
   B200_REQUIRE((((uintptr_t)dlogits_dev) & 15) == 0, "mlp_backward_tc: dlogits must be 16-byte aligned");
   BwdPlan bp;
   bwd_plan(batch, hidden, &bp);
-  size_t need = (size_t)bp.splits * hidden * 32 * sizeof(float);
+  size_t need = (size_t)bp.splits * hidden * 32 * sizeof(float) + (size_t)bp.splits * sizeof(float);
   B200_REQUIRE(scratch_dev && scratch_bytes >= need, "mlp_backward_tc: scratch too small (%zu < %zu)", scratch_bytes, need);
   Layout L{n_features, hidden};
   cudaStream_t st = as_stream(stream);
@@ -599,14 +670,15 @@ int b200ds_mlp_backward_tc(const void* xq_dev, const void* wq_dev, const float* 
     attr_set[dev & 63] = true;
   }
   const unsigned char* w1q = reinterpret_cast<const unsigned char*>(wq_dev);
+  float* db2_part = reinterpret_cast<float*>(scratch_dev) + (size_t)bp.splits * hidden * 32;
   mlp_bwd_tc_kernel<<<bp.groups * bp.splits, kBwdThreads, bp.smem, st>>>(
-      reinterpret_cast<const unsigned char*>(xq_dev), w1q, dlogits_dev, reinterpret_cast<float*>(scratch_dev), bp.n_btiles,
-      hidden, bp.nb, bp.groups, bp.splits);
+      reinterpret_cast<const unsigned char*>(xq_dev), w1q, dlogits_dev, reinterpret_cast<float*>(scratch_dev), db2_part,
+      bp.n_btiles, hidden, bp.nb, bp.groups, bp.splits);
   B200_LAUNCH_CHECK();
   int fgrid = (hidden + 7) / 8;
   if (fgrid > sm_count() * 8) fgrid = sm_count() * 8;
-  mlp_bwd_tc_finish<<<fgrid, 256, 0, st>>>(reinterpret_cast<const float*>(scratch_dev), bp.splits, params_dev, dlogits_dev,
-                                           batch, L, grads_dev);
+  mlp_bwd_tc_finish<<<fgrid, 256, 0, st>>>(reinterpret_cast<const float*>(scratch_dev), db2_part, bp.splits, params_dev, L,
+                                           grads_dev);
   B200_LAUNCH_CHECK();
   return B200DS_OK;
 }

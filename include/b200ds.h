@@ -192,15 +192,18 @@ B200DS_API int b200ds_mlp_backward_tc(const void* xq_dev, const void* wq_dev, co
  * forward, loss, backward, all-reduce, Adam (t = step0 + 1), D2H of the loss, and a
  * stream synchronise (this is the one entry point that blocks the host, as loss.item()
  * does at train.py:115).  Shapes inside the tiny class (F <= 32, H <= 256, batch <= 32)
- * take the fused one-launch kernel, others the per-stage fp32 kernels.
- * The caller supplies every device buffer in `bufs` (all borrowed, fp32):
- *   scratch: b200ds_train_step_scratch_bytes(...) bytes, zeroed once by the caller. */
+ * take the fused one-launch kernel; shapes of the tensor-core class take the bf16 tcgen05
+ * kernels when `xq` and `wq` are supplied (non-NULL); everything else the per-stage fp32
+ * kernels.  The caller supplies every device buffer in `bufs` (all borrowed):
+ *   scratch: b200ds_train_step_scratch_bytes(...) bytes, zeroed once by the caller;
+ *   xq / wq: b200ds_tc_xq_bytes(batch) / b200ds_tc_wq_bytes(H) bytes, or NULL for fp32. */
 typedef struct b200ds_step_bufs {
   float* params;  float* grads;  float* exp_avg;  float* exp_avg_sq;   /* flat, length padded to 4 */
   float* x_stage; float* y_stage;          /* [batch*F], [batch] device staging */
   float* logits;  float* dlogits;          /* [batch] */
   float* loss;                             /* 1 float */
   void* scratch;  size_t scratch_bytes;
+  void* xq;  void* wq;                     /* bf16 operand packs, or NULL */
 } b200ds_step_bufs;
 B200DS_API size_t b200ds_train_step_scratch_bytes(int64_t batch, int n_features, int hidden);
 B200DS_API int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* bufs,

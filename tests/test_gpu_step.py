@@ -295,7 +295,7 @@ def test_host_buffer_step_both_paths(lib, cuda_dev):
         xs, ys, lg, dl, ls = z(B * F), z(B), z(B), z(B), z(1)
         sc = torch.zeros(max(256, lib.b200ds_train_step_scratch_bytes(B, F, H)), dtype=torch.uint8, device=cuda_dev)
         bufs = _lib.StepBufs(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), xs.data_ptr(), ys.data_ptr(),
-                             lg.data_ptr(), dl.data_ptr(), ls.data_ptr(), sc.data_ptr(), sc.numel())
+                             lg.data_ptr(), dl.data_ptr(), ls.data_ptr(), sc.data_ptr(), sc.numel(), None, None)
         ctx = C.c_void_p()
         _check(lib, lib.b200ds_ctx_create(0, 0, 1, None, C.byref(ctx)))
         flat = ora.flatten(p)

@@ -118,3 +118,64 @@ def test_tc_matches_fp32_path_within_bf16_tolerance(lib, cuda_dev):
     torch.cuda.synchronize()
     assert abs(float(l16) - float(l32)) <= 2e-2 * abs(float(l32))
     assert float((z16 - z32).abs().max()) <= 2e-2 * float(z32.abs().max())
+
+
+def test_engine_bf16_config_trains_within_tolerance(cuda_dev):
+    """bf16.enabled in the engine config routes engine(x)/backward through the tcgen05
+    kernels; N steps must track the oracle's bf16 restatement within 2e-2 (north_star)."""
+    import b200ds
+    F, H, B, steps = 20, 256, 256, 12
+    torch.manual_seed(11)
+    net = torch.nn.Sequential(torch.nn.Linear(F, H), torch.nn.ReLU(), torch.nn.Linear(H, 1))
+    p = {"w1": net[0].weight.detach().clone(), "b1": net[0].bias.detach().clone(),
+         "w2": net[2].weight.detach().clone(), "b2": net[2].bias.detach().clone()}
+    opt = torch.optim.Adam(net.parameters(), lr=1e-3)
+    cfg = {"train_batch_size": B, "gradient_accumulation_steps": 1, "bf16": {"enabled": True}, "zero_optimization": {"stage": 0}}
+    engine, _, _, _ = b200ds.initialize(model=net, optimizer=opt, config=cfg)
+    crit = b200ds.BCEWithLogitsLoss()
+    flat = ora.flatten(p)
+    st = ora.AdamState()
+    for s in range(steps):
+        x = torch.randn(B, F)
+        y = ora.label_rule(x)
+        loss = crit(engine(x.to(cuda_dev)), y.to(cuda_dev))
+        engine.backward(loss)
+        engine.step()
+        assert engine._tc
+        pp = ora.unflatten(flat, F, H)
+        lref, g = ora._bf16_step(pp, x, y)
+        ora.adam_update(flat, ora.flatten(g), st, 1e-3)
+        assert abs(loss.item() - float(lref)) <= 2e-2 * abs(float(lref)), s
+    got = engine.flat[: engine.P].cpu()
+    assert float((got - flat).abs().max()) <= 2e-2 * float(flat.abs().max())
+
+
+def test_host_buffer_step_tc_path(lib, cuda_dev):
+    from b200ds import _lib
+    B, F, H = 512, 20, 256
+    torch.manual_seed(5)
+    p = ora.init_params(F, H)
+    flat = ora.flatten(p)
+    P = flat.numel(); Ppad = (P + 3) // 4 * 4
+    z = lambda n: torch.zeros(n, dtype=torch.float32, device=cuda_dev)      # noqa: E731
+    params = z(Ppad); params[:P] = flat.to(cuda_dev)
+    grads, m, v, xs, ys, lg, dl, ls = z(Ppad), z(Ppad), z(Ppad), z(B * F), z(B), z(B), z(B), z(1)
+    sc = torch.zeros(max(256, lib.b200ds_train_step_scratch_bytes(B, F, H)), dtype=torch.uint8, device=cuda_dev)
+    xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=cuda_dev)
+    wq = torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=cuda_dev)
+    bufs = _lib.StepBufs(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), xs.data_ptr(), ys.data_ptr(),
+                         lg.data_ptr(), dl.data_ptr(), ls.data_ptr(), sc.data_ptr(), sc.numel(), xq.data_ptr(), wq.data_ptr())
+    ctx = C.c_void_p()
+    _chk(lib.b200ds_ctx_create(0, 0, 1, None, C.byref(ctx)))
+    st = ora.AdamState()
+    xh = torch.empty(B, F).pin_memory(); yh = torch.empty(B).pin_memory(); lh = torch.zeros(1).pin_memory()
+    for step in range(3):
+        xh.copy_(torch.randn(B, F)); yh.copy_(ora.label_rule(xh).reshape(-1))
+        pp = ora.unflatten(flat, F, H)
+        lref, g = ora._bf16_step(pp, xh.clone(), yh.reshape(-1, 1).clone())
+        ora.adam_update(flat, ora.flatten(g), st, 1e-3)
+        _chk(lib.b200ds_train_step_host(ctx, C.byref(bufs), xh.data_ptr(), yh.data_ptr(), B, F, H, 1e-3, 0.9, 0.999, 1e-8,
+                                        step, lh.data_ptr(), _st()))
+        assert abs(float(lh) - float(lref)) <= 2e-2 * abs(float(lref)), step
+    assert float((params[:P].cpu() - flat).abs().max()) <= 2e-2 * float(flat.abs().max())
+    _chk(lib.b200ds_ctx_destroy(ctx))

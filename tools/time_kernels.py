@@ -1,0 +1,37 @@
+#!/usr/bin/env python3
+"""Time the tensor-core forward/backward kernels alone (CUDA events, after warm-up)."""
+import ctypes as C, os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "distributed-gpu-test_b200"))
+import torch
+from b200ds import _lib
+lib = _lib.load()
+B, F, H = int(os.environ.get("B", 65536)), 20, int(os.environ.get("H", 4096))
+dev = torch.device("cuda", 0)
+torch.manual_seed(0)
+P = F * H + 2 * H + 1; Ppad = (P + 3) // 4 * 4
+params = torch.randn(Ppad, device=dev) * 0.1
+x = torch.randn(B, F, device=dev)
+dz = torch.randn(B, device=dev) * 1e-5
+xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=dev)
+wq = torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=dev)
+z = torch.empty(B, device=dev); g = torch.empty(Ppad, device=dev)
+sc = torch.zeros(lib.b200ds_mlp_backward_tc_scratch_bytes(B, F, H), dtype=torch.uint8, device=dev)
+st = torch.cuda.current_stream().cuda_stream
+_lib.check(lib.b200ds_pack_x_bf16(x.data_ptr(), B, F, xq.data_ptr(), st))
+_lib.check(lib.b200ds_pack_params_bf16(params.data_ptr(), F, H, wq.data_ptr(), st))
+def fwd(): _lib.check(lib.b200ds_mlp_forward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), B, F, H, z.data_ptr(), st))
+def bwd(): _lib.check(lib.b200ds_mlp_backward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), dz.data_ptr(), B, F, H, g.data_ptr(), sc.data_ptr(), sc.numel(), st))
+# spin the clocks up
+t0 = time.time()
+while time.time() - t0 < 1.0:
+    fwd(); bwd()
+torch.cuda.synchronize()
+for name, fn in (("fwd", fwd), ("bwd+finish", bwd)):
+    for _ in range(5): fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n = 50
+    e0.record()
+    for _ in range(n): fn()
+    e1.record(); torch.cuda.synchronize()
+    print(f"{os.environ.get('B200DS_LIB','default'):28s} B={B} H={H} {name:11s} {1e3 * e0.elapsed_time(e1) / n:8.2f} us", flush=True)
