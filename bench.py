@@ -57,6 +57,12 @@ def peaks():
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sus=1400.0, src="fallback")   # B200_PROFILING.md fallback
 
 
+def trace(msg):
+    if os.environ.get("B200DS_BENCH_TRACE"):
+        sys.stderr.write(f"[bench rank {os.environ.get('RANK', 0)}] {msg}\n")
+        sys.stderr.flush()
+
+
 def init_flat(F, H):
     """Initial weights in the reference's creation order (train.py:54,76): seed, then the two
     nn.Linear default inits; flat layout [W1|b1|W2|b2]."""
@@ -204,9 +210,9 @@ class WideStep:
     def step(self, st, ev_pair=None):
         lib, chk = self.lib, self._lib.check
         B, F, H = self.B, self.F, self.H
-        adv = C.c_uint64(0)
-        chk(lib.b200ds_philox_normal(self.x.data_ptr(), B * F, self.seed, self.offset, C.byref(adv), st))
-        self.offset += adv.value
+        # the draw index is the device step counter (incremented by the loss kernel), so the same
+        # launch sequence can be replayed from a CUDA graph and still get a fresh batch each step
+        chk(lib.b200ds_philox_normal_counted(self.x.data_ptr(), B * F, self.seed, 0, self.counter.data_ptr(), st))
         chk(lib.b200ds_label_rule(self.x.data_ptr(), self.y.data_ptr(), B, F, st))
         if self.tc:
             chk(lib.b200ds_pack_x_bf16(self.x.data_ptr(), B, F, self.xq.data_ptr(), st))
@@ -274,19 +280,37 @@ def run_ours(a):
     else:
         ws = WideStep(lib, ctx, dev, wl, world, rank, precision)
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
-        for _ in range(max(3, a.warmup)):
+        W = max(3, a.warmup)
+        for _ in range(W):
             ws.step(st)
         barrier()
+        trace("eager warm-up done")
+        # ---- the step as ONE CUDA graph (kernels + the side-stream all-reduce): no per-kernel launch cost
+        graph = torch.cuda.CUDAGraph()
+        cap = torch.cuda.Stream(device=dev)
+        cap.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.graph(graph, stream=cap):
+            ws.step(torch.cuda.current_stream().cuda_stream)
+        torch.cuda.current_stream().wait_stream(cap)
+        trace("graph captured")
+        graph.replay()
+        torch.cuda.synchronize()
+        trace("first replay done")
+        # untimed: let the SM clock settle under load.  A FIXED replay count: every replay holds a
+        # collective, so all ranks must run the same number of them.
+        for _ in range(4000 if wl["H"] <= 4096 else 2000):
+            graph.replay()
+        barrier()
+        trace("clock warm-up replays done")
         K = a.steps
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-        kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
         clk = ClockSampler(local)
         clk.start()
         wall0 = time.perf_counter()
         for i in range(K):
             flush.fill_(i & 0xFF)                 # L2 flush between timed steps, outside the event bracket
             evs[i][0].record()
-            ws.step(st, kev[i])
+            graph.replay()
             evs[i][1].record()
             if i % 8 == 7:
                 clk.sample()
@@ -294,8 +318,16 @@ def run_ours(a):
         barrier()
         wall = time.perf_counter() - wall0
         clk.stop()
+        trace("timed region done")
         dev_ms = sum(e0.elapsed_time(e1) for e0, e1 in evs)
-        k_ms = sum(e0.elapsed_time(e1) for e0, e1 in kev) / K
+        # ---- dominant kernel: same step launched eagerly, CUDA events around that kernel alone
+        K2 = max(3, min(K, 10))
+        kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K2)]
+        for i in range(K2):
+            flush.fill_(i & 0xFF)
+            ws.step(st, kev[i])
+        torch.cuda.synchronize()
+        k_ms = sum(e0.elapsed_time(e1) for e0, e1 in kev) / K2
         t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -306,16 +338,22 @@ def run_ours(a):
         achieved = ws.dominant_flops() / (k_ms / 1e3) / 1e12
         roof = dict(bound="tensor", achieved=achieved, peak=pk["tf_sus"], unit="TFLOP/s", frac=achieved / pk["tf_sus"],
                     traffic=None, kernel=ws.dominant["name"], kernel_ms=k_ms, peak_source=f"{pk['src']} bf16 sustained",
-                    step_frac=step_flops(**wl) / (ms_per_step / 1e3) / 1e12 / pk["tf_sus"])
+                    step_frac=step_flops(**wl) / (ms_per_step / 1e3) / 1e12 / pk["tf_sus"],
+                    note="kernel_ms: CUDA events around the kernel in an eager pass of the same step right after the timed region")
         # ---- e2e: the C-ABI host-buffer call, H2D/D2H inside the timed region
+        graph.reset()          # NCCL will not tear a communicator down while a captured graph still refers to it
+        del graph
+        trace("kernel pass done")
         e2e = bench_e2e(lib, ctx, dev, wl, world, a, barrier, precision)
+        trace("e2e done")
         out.update(dict(value=value, ms_per_step=ms_per_step, roofline=roof, e2e=e2e, clocks=clk.summary(),
                         gpu_launches=K * ws.launches_per_step, wall_s=wall, loss_last=loss_last,
                         config={"workload": f"{a.workload}: train.py step, F={wl['F']} H={wl['H']}, {wl['B']} samples/GPU/step "
                                             f"generated on device (Philox4x32-10), Adam, {world} rank(s)",
                                 "per_gpu_batch": wl["B"], "n_features": wl["F"], "hidden": wl["H"], "parallelism": f"dp{world}",
                                 "l2": "256 MiB device buffer rewritten between timed steps, outside the per-step CUDA-event brackets",
-                                "timing": "sum of per-step CUDA-event times on the launching stream, max over ranks"},
+                                "timing": "each step = one CUDA-graph replay of the whole step (all kernels + NCCL all-reduce), "
+                                          "bracketed by CUDA events on the launching stream; sum over steps, max over ranks"},
                         dtype="f32" if precision == "fp32" else "bf16"))
         if not a.no_tiny and rank == 0 and world == 1:
             try:

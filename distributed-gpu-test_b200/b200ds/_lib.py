@@ -41,6 +41,7 @@ PROTOTYPES = {
     "b200ds_ctx_destroy": (C.c_int, [c_ptr]),
     "b200ds_ctx_info": (C.c_int, [c_ptr, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "b200ds_philox_normal": (C.c_int, [c_ptr, c_i64, c_u64, c_u64, C.POINTER(c_u64), c_stream]),
+    "b200ds_philox_normal_counted": (C.c_int, [c_ptr, c_i64, c_u64, c_u64, c_ptr, c_stream]),
     "b200ds_label_rule": (C.c_int, [c_ptr, c_ptr, c_i64, C.c_int, c_stream]),
     "b200ds_gather_batch": (C.c_int, [c_ptr, c_ptr, c_ptr, c_i64, C.c_int, c_ptr, c_ptr, c_stream]),
     "b200ds_mlp_forward_f32": (C.c_int, [c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_stream]),

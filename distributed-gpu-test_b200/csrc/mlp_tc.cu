@@ -140,27 +140,37 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
     for (int i = 0; i < kFwdXStages; ++i) { mbar_init(&sh->x_full[i], 1); mbar_init(&sh->x_free[i], n_issuers); }
     for (int i = 0; i < kFwdRing; ++i) { mbar_init(&sh->d1_full[i], 1); mbar_init(&sh->d1_free[i], kFwdEpiWarps); }
     mbar_fence_init();
+    // start the 128 KB W1 slice right away: it overlaps the rest of the prologue
+    const unsigned char* wsrc = w1q + (size_t)slice * slice_rows * KP * 2;
+    mbar_arrive_expect_tx(&sh->w_bar, (uint32_t)slice_rows * KP * 2);
+    for (int c = 0; c < NC; ++c) tma_load_1d(w1s + (size_t)c * kTileBytes, wsrc + (size_t)c * kTileBytes, kTileBytes, &sh->w_bar);
   }
   if (warp == 1) tmem_alloc<512>(&sh->tmem_slot);
   for (int i = threadIdx.x; i < slice_rows; i += blockDim.x) w2s[i] = w2[slice * slice_rows + i];
-  if (threadIdx.x < 32) {      // v = sum over the 64-row blocks of this slice, fixed order
+  {      // v = sum over the 64-row blocks of this slice: 8 warps take 1/8 of the blocks each, then a fixed-order sum
     const int nblk = slice_rows / kPackRows;
-    const float* vp = vlin + (size_t)slice * nblk * 32 + threadIdx.x;
-    float a = 0.f;
-    for (int i = 0; i < nblk; ++i) a += vp[(size_t)i * 32];
-    sh->v[threadIdx.x] = a;
+    if (warp < 8) {
+      const float* vp = vlin + (size_t)slice * nblk * 32 + lane;
+      float a = 0.f;
+      for (int i = warp; i < nblk; i += 8) a += vp[(size_t)i * 32];
+      sh->red[0][0][warp * 32 + lane] = a;      // red[] is free until the first tile ends
+    }
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if (threadIdx.x < 32) {
+    float a = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) a += (&sh->red[0][0][0])[w * 32 + threadIdx.x];
+    sh->v[threadIdx.x] = a;
+  }
+  __syncthreads();
   const uint32_t tmem = sh->tmem_slot;
 
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      const unsigned char* wsrc = w1q + (size_t)slice * slice_rows * KP * 2;
-      mbar_arrive_expect_tx(&sh->w_bar, (uint32_t)slice_rows * KP * 2);
-      for (int c = 0; c < NC; ++c) tma_load_1d(w1s + (size_t)c * kTileBytes, wsrc + (size_t)c * kTileBytes, kTileBytes, &sh->w_bar);
       int s = 0; uint32_t ph = 0;
       for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice) {
         mbar_wait(&sh->x_free[s], ph ^ 1);
@@ -235,35 +245,34 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
       float acc[64];
 #pragma unroll
       for (int i = 0; i < 64; ++i) acc[i] = 0.f;
-      for (int c = 0; c < NC; ++c, ++q) {
-#if defined(B200DS_ABLATE) && B200DS_ABLATE >= 3
-        continue;
-#endif
+      // Software pipeline across chunks: the TMEM load of one 32-column piece is always in flight
+      // while the FFMAs of the previous piece issue (va: columns 0-31 of the chunk, vb: 32-63).
+      uint32_t va[32], vb[32];
+      {
         const int r = q % kFwdRing;
-        const uint32_t rph = (uint32_t)(q / kFwdRing) & 1u;
-        const float w2n = w2s[c * kTileRows + quad * 32 + lane];
-        const uint32_t tbase = tmem + lane_base + r * 128 + half * 64;
-        mbar_wait(&sh->d1_full[r], rph);
+        mbar_wait(&sh->d1_full[r], (uint32_t)(q / kFwdRing) & 1u);
         tc_fence_after();
-        uint32_t va[32], vb[32];
-#if !defined(B200DS_ABLATE) || B200DS_ABLATE < 2
-        tmem_ld32(tbase, va);
-        tmem_ld32(tbase + 32, vb);
-        tmem_wait_ld();
-#else
-        for (int i = 0; i < 32; ++i) { va[i] = tbase + i; vb[i] = tbase - i; }
-#endif
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sh->d1_free[r]);     // the chunk is in registers: the buffer can be refilled
-#if !defined(B200DS_ABLATE) || B200DS_ABLATE < 1
+        tmem_ld32(tmem + lane_base + r * 128 + half * 64, va);
+      }
+      for (int c = 0; c < NC; ++c, ++q) {
+        const int r = q % kFwdRing;
+        const float w2n = w2s[c * kTileRows + quad * 32 + lane];
+        tmem_wait_ld();                                              // va (piece 0 of chunk q) has landed
+        tmem_ld32(tmem + lane_base + r * 128 + half * 64 + 32, vb);  // piece 1 of chunk q
 #pragma unroll
         for (int i = 0; i < 32; ++i) acc[i] = fmaf(fabsf(__uint_as_float(va[i])), w2n, acc[i]);
+        tmem_wait_ld();                                              // vb has landed: the buffer is fully read
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sh->d1_free[r]);
+        if (c + 1 < NC) {                                            // piece 0 of chunk q+1
+          const int r1 = (q + 1) % kFwdRing;
+          mbar_wait(&sh->d1_full[r1], (uint32_t)((q + 1) / kFwdRing) & 1u);
+          tc_fence_after();
+          tmem_ld32(tmem + lane_base + r1 * 128 + half * 64, va);
+        }
 #pragma unroll
         for (int i = 0; i < 32; ++i) acc[32 + i] = fmaf(fabsf(__uint_as_float(vb[i])), w2n, acc[32 + i]);
-#else
-        acc[0] += __uint_as_float(va[0] ^ vb[1]) * w2n;
-#endif
       }
       // ---- sum over n: 32 lanes by a transposing butterfly, then the 4 quadrants through smem
       lane_fold<64, 16>(acc, lane);

@@ -45,7 +45,11 @@ __device__ __forceinline__ float2 box_muller(unsigned a, unsigned b) {
 
 // One thread = one Philox subsequence, exactly as ATen launches it.
 __global__ void __launch_bounds__(256) philox_normal_kernel(float* __restrict__ out, int64_t numel,
-                                                            uint2 key, uint64_t ctr0, int calls) {
+                                                            uint2 key, uint64_t ctr0, int calls,
+                                                            const unsigned long long* __restrict__ step_counter) {
+  // graph-replayable form: the draw index lives in device memory and every draw advances the
+  // Philox counter by `calls`, exactly like consecutive torch.randn calls on one generator
+  if (step_counter) ctr0 += (uint64_t)(*step_counter) * (uint64_t)calls;
   const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   for (int c = 0; c < calls; ++c) {
@@ -106,9 +110,23 @@ int b200ds_philox_normal(float* x_dev, int64_t numel, uint64_t seed, uint64_t of
   int grid, calls;
   philox_plan(numel, &grid, &calls);
   philox_normal_kernel<<<grid, 256, 0, as_stream(stream)>>>(
-      x_dev, numel, make_uint2((unsigned)seed, (unsigned)(seed >> 32)), offset / 4, calls);
+      x_dev, numel, make_uint2((unsigned)seed, (unsigned)(seed >> 32)), offset / 4, calls, nullptr);
   B200_LAUNCH_CHECK();
   if (offset_advance) *offset_advance = (uint64_t)calls * 4;
+  return B200DS_OK;
+}
+
+int b200ds_philox_normal_counted(float* x_dev, int64_t numel, uint64_t seed, uint64_t offset0,
+                                 const uint64_t* draw_counter_dev, uintptr_t stream) {
+  B200_REQUIRE(numel > 0 && x_dev != nullptr, "philox_normal_counted: empty or null output");
+  B200_REQUIRE(offset0 % 4 == 0, "philox_normal_counted: offset0 must be a multiple of 4");
+  B200_REQUIRE(draw_counter_dev != nullptr, "philox_normal_counted: null draw counter");
+  int grid, calls;
+  philox_plan(numel, &grid, &calls);
+  philox_normal_kernel<<<grid, 256, 0, as_stream(stream)>>>(
+      x_dev, numel, make_uint2((unsigned)seed, (unsigned)(seed >> 32)), offset0 / 4, calls,
+      reinterpret_cast<const unsigned long long*>(draw_counter_dev));
+  B200_LAUNCH_CHECK();
   return B200DS_OK;
 }
 

@@ -72,6 +72,11 @@ B200DS_API int b200ds_ctx_info(const b200ds_ctx* ctx, int* device, int* rank, in
  * offset moves, as torch's CUDA generator would. */
 B200DS_API int b200ds_philox_normal(float* x_dev, int64_t numel, uint64_t seed, uint64_t offset,
                          uint64_t* offset_advance, uintptr_t stream);
+/* Same stream, CUDA-graph friendly: the k-th replay (k = *draw_counter_dev, a device uint64
+ * the caller's step increments, e.g. the step counter of b200ds_bce_loss_grad) produces what
+ * the (k+1)-th consecutive torch.randn(numel) call after (seed, offset0) would. */
+B200DS_API int b200ds_philox_normal_counted(float* x_dev, int64_t numel, uint64_t seed, uint64_t offset0,
+                                            const uint64_t* draw_counter_dev, uintptr_t stream);
 /* y[b] = 1 if sum_{j < F/2} x[b,j] > 0 else 0   (train.py:22-23) */
 B200DS_API int b200ds_label_rule(const float* x_dev, float* y_dev, int64_t batch, int n_features,
                       uintptr_t stream);
