@@ -99,7 +99,9 @@ pack_w1_kernel(const float* __restrict__ params, Layout L, uint4* __restrict__ w
 constexpr int kFwdXStages = 3;
 constexpr int kFwdRing = 4;               // D1T accumulators in TMEM: 4 x 128 columns
 constexpr int kFwdEpiWarps = 8;           // warp (quad, half): 32 lanes (n) x 64 columns (b)
-constexpr int kFwdThreads = 32 * 11;      // warp 0 TMA, warp 1 / warp 10 MMA (even / odd chunks), warps 2-9 epilogue
+constexpr int kFwdThreads = 32 * 11;      // warps 0-7 epilogue, warp 8 TMA, warps 9 / 10 MMA (even / odd chunks).
+                                          // The issuing warps sit at the highest warp ids: the SM's arbiter favours the
+                                          // highest ready warp, and an MMA issuer that waits behind 64 FFMAs stalls the pipe.
 
 struct FwdSmem {                           // fixed-size tail after the W1 slice / w2 slice / x stages
   float v[32];
@@ -145,7 +147,7 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
     mbar_arrive_expect_tx(&sh->w_bar, (uint32_t)slice_rows * KP * 2);
     for (int c = 0; c < NC; ++c) tma_load_1d(w1s + (size_t)c * kTileBytes, wsrc + (size_t)c * kTileBytes, kTileBytes, &sh->w_bar);
   }
-  if (warp == 1) tmem_alloc<512>(&sh->tmem_slot);
+  if (warp == 9) tmem_alloc<512>(&sh->tmem_slot);
   for (int i = threadIdx.x; i < slice_rows; i += blockDim.x) w2s[i] = w2[slice * slice_rows + i];
   {      // v = sum over the 64-row blocks of this slice: 8 warps take 1/8 of the blocks each, then a fixed-order sum
     const int nblk = slice_rows / kPackRows;
@@ -168,7 +170,7 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
   __syncthreads();
   const uint32_t tmem = sh->tmem_slot;
 
-  if (warp == 0) {
+  if (warp == 8) {
     // ===== TMA producer =====
     if (lane == 0) {
       int s = 0; uint32_t ph = 0;
@@ -179,11 +181,11 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         if (++s == kFwdXStages) { s = 0; ph ^= 1; }
       }
     }
-  } else if (warp == 1 || warp == 10) {
+  } else if (warp == 9 || warp == 10) {
     // ===== MMA issuers (chunk parity): D1T[ring] = w1_chunk . x_tile^T, K = 32.  The whole warp
     // walks the loop (uniform control flow); one elected lane issues.  Two issuing warps because
     // one warp's wait + issue + commit round is longer than the 132 cycles a chunk executes. =====
-    const int me = warp == 1 ? 0 : 1;
+    const int me = warp - 9;
     if (me < NC) {
       const uint32_t idesc = idesc_bf16(128, 128, 0, 0);
       const uint64_t xdesc0 = smem_desc(smem_u32(xs), LBO_K, SBO_K);
@@ -219,7 +221,7 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
     }
   } else {
     // ===== epilogue: 8 warps on every chunk =====
-    const int half = (warp - 2) >> 2, quad = warp & 3;
+    const int half = warp >> 2, quad = warp & 3;
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     const int row = quad * 32 + lane;                      // the b row this thread finishes (half 0 warps only)
     const float b2 = slice == 0 ? b2p[0] : 0.f;
@@ -297,14 +299,15 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<512>(tmem);
+  if (warp == 9) tmem_dealloc<512>(tmem);
 }
 
 // ------------------------------------------------------------------ backward
 constexpr int kBwdXStages = 4;
 constexpr int kBwdRing = 3;               // D1T accumulators: 3 x 128 columns (cols 0..383)
 constexpr int kBwdNB = 4;                 // n blocks per CTA: S accumulators 4 x 32 columns (cols 384..511)
-constexpr int kBwdThreads = 32 * 12;      // 0 TMA + dz stager, 1 MMA1, 2-3 MMA2 (n block parity), 4-11 epilogue (two groups)
+constexpr int kBwdThreads = 32 * 12;      // 0-7 epilogue (two groups), 8 TMA + dz stager, 9 MMA1, 10-11 MMA2 (n block parity);
+                                          // issuers at the highest warp ids, see the forward kernel
 
 struct BwdSmem {
   uint32_t dzs[kBwdXStages][64];          // dz of the tile as bf16x2 pairs
@@ -335,14 +338,14 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
     mbar_init(&sh->s_full, n_issuers);
     mbar_fence_init();
   }
-  if (warp == 1) tmem_alloc<512>(&sh->tmem_slot);
+  if (warp == 9) tmem_alloc<512>(&sh->tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = sh->tmem_slot;
   const uint32_t s_col0 = kBwdRing * 128;
 
-  if (warp == 0) {
+  if (warp == 8) {
     // ===== TMA producer (lane 0) + dz stager (all lanes): dz[b0..b0+127] -> bf16x2 pairs in smem =====
     if (lane == 0) {
       const unsigned char* wsrc = w1q + (size_t)group * nb * kTileBytes;
@@ -368,7 +371,7 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
     }
     dsum = warp_sum(dsum);       // this split's share of db2 = sum_b dz[b]
     if (group == 0 && lane == 0) db2_part[split] = dsum;
-  } else if (warp == 1) {
+  } else if (warp == 9) {
     // ===== MMA1 issuer: D1T[ring] = w1_block . x_tile^T (lanes = n, columns = b) =====
     {
       const uint32_t idesc = idesc_bf16(128, 128, 0, 0);
@@ -395,11 +398,11 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         if (++s == kBwdXStages) { s = 0; xph ^= 1; }
       }
     }
-  } else if (warp == 2 || warp == 3) {
+  } else if (warp == 10 || warp == 11) {
     // ===== MMA2 issuers: S[i] += A2[ring] (TMEM, bf16) . x_tile (MN-major view), K = 128 rows of b.
     // n block i belongs to issuer i % 2 for the whole kernel, so the accumulation order into
     // S[i] is that thread's program order; two issuing threads lift the per-thread issue rate.
-    const int me = warp - 2;
+    const int me = warp - 10;
     if (me < nb) {
       const uint32_t idesc = idesc_bf16(128, 32, 0, 1);
       const uint64_t gdesc0 = smem_desc(smem_u32(xs), /*LBO = K groups*/ SBO_K, /*SBO = N groups*/ LBO_K);
@@ -432,7 +435,7 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
     }
   } else {
     // ===== epilogue: mask * dz -> bf16, in place; chunk q goes to group q % 2 =====
-    const int ew = warp - 4, grp = ew >> 2, quad = warp & 3;
+    const int grp = warp >> 2, quad = warp & 3;
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     int q = 0;
     int s = 0; uint32_t xph = 0;
@@ -502,7 +505,7 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<512>(tmem);
+  if (warp == 9) tmem_dealloc<512>(tmem);
 }
 
 // grads from S: one warp per hidden unit n, lane = k; split partials summed in split order
