@@ -47,6 +47,7 @@ PROTOTYPES = {
     "b200ds_mlp_forward_f32": (C.c_int, [c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_stream]),
     "b200ds_bce_scratch_bytes": (C.c_size_t, [c_i64]),
     "b200ds_bce_loss_grad": (C.c_int, [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, C.c_size_t, c_stream]),
+    "b200ds_bce_loss_grad_noalloc": (C.c_int, [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_stream]),
     "b200ds_mlp_backward_f32_scratch_bytes": (C.c_size_t, [c_i64, C.c_int, C.c_int]),
     "b200ds_mlp_backward_f32": (C.c_int, [c_ptr, c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_ptr, C.c_size_t, c_stream]),
     "b200ds_allreduce_bucket": (C.c_int, [c_ptr, c_ptr, c_i64, c_stream]),

@@ -93,6 +93,17 @@ bce_loss_grad_kernel(const float* __restrict__ z, const float* __restrict__ y, i
   }
 }
 
+// ---- scratch for the allocation-free entry point -------------------------------------
+// Lives in the library image: every GPU that loads libb200ds.so carries these 1280 bytes
+// until the process exits.  256 per-CTA partial sums + the arrival ticket; the prefix of the
+// layout is the same as LossScratch, so the kernel above runs on it unchanged as long as the
+// grid has at most kStaticLossMaxBlocks CTAs.
+constexpr int kStaticLossMaxBlocks = 256;
+constexpr int64_t kStaticLossMaxBatch = 4194304;     // 2^22 rows: 4 rows per thread per pass, 16 passes at most
+constexpr size_t kStaticLossBytes = 1280;
+static_assert(16 + kStaticLossMaxBlocks * sizeof(float) <= kStaticLossBytes, "static loss scratch too small");
+static __device__ __align__(256) unsigned char g_static_loss_scratch[kStaticLossBytes];
+
 }  // namespace b200ds
 
 using namespace b200ds;
@@ -114,6 +125,48 @@ int b200ds_bce_loss_grad(const float* logits_dev, const float* y_dev, int64_t ba
   bce_loss_grad_kernel<<<grid, kLossThreads, 0, as_stream(stream)>>>(
       logits_dev, y_dev, batch, loss_dev, dlogits_dev,
       reinterpret_cast<unsigned long long*>(step_counter_dev), reinterpret_cast<LossScratch*>(scratch_dev));
+  B200_LAUNCH_CHECK();
+  return B200DS_OK;
+}
+
+// The same loss + gradient pass for callers that have no way to hand over device scratch.
+// Two kinds of caller of this library are in that position: a launcher or plugin host written
+// against the C ABI alone (it holds the tensors the framework gave it and has no allocator
+// of its own to ask for more), and a step loop running under a framework whose caching
+// allocator already owns the GPU's memory, where a raw cudaMalloc from a plugin can fail or
+// stall the device mid-step.  Nothing is allocated or freed here, on any path.
+//
+// The scratch is the file-scope device array above.  Its device address is looked up once per
+// device, by the first call made while that device is current (cudaGetSymbolAddress); make
+// that first call outside of any stream capture.  Because the array is shared by every call
+// and keeps whatever the previous call left in it, the arrival ticket is cleared on `stream`
+// before each launch; two calls whose GPU work overlaps (different streams, no ordering
+// between them) would race on it and must be serialised by the caller.
+int b200ds_bce_loss_grad_noalloc(const float* logits_dev, const float* y_dev, int64_t batch,
+                                 float* loss_dev, float* dlogits_dev, uint64_t* step_counter_dev,
+                                 uintptr_t stream) {
+  B200_REQUIRE(batch > 0, "bce_loss_grad_noalloc: batch must be positive (got %lld)", (long long)batch);
+  B200_REQUIRE(batch <= kStaticLossMaxBatch,
+               "bce_loss_grad_noalloc: batch %lld exceeds the built-in scratch limit of %lld rows; "
+               "use b200ds_bce_loss_grad with caller scratch", (long long)batch, (long long)kStaticLossMaxBatch);
+  B200_REQUIRE(logits_dev && y_dev && loss_dev, "bce_loss_grad_noalloc: null pointer");
+  static void* scratch_of_device[64];
+  int dev = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < 64, "bce_loss_grad_noalloc: device index %d out of range", dev);
+  if (scratch_of_device[dev] == nullptr) {
+    // the array's name is only a host-side handle; the kernel needs the address on THIS device
+    void* p = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(&p, g_static_loss_scratch));
+    scratch_of_device[dev] = p;
+  }
+  LossScratch* scr = reinterpret_cast<LossScratch*>(scratch_of_device[dev]);
+  cudaStream_t st = as_stream(stream);
+  int64_t want = (batch / 4 + kLossThreads - 1) / kLossThreads;
+  int grid = (int)(want < 1 ? 1 : (want > kStaticLossMaxBlocks ? kStaticLossMaxBlocks : want));
+  B200_CUDA(cudaMemsetAsync(scr, 0, 16, st));      // ticket must start at zero whatever ran before
+  bce_loss_grad_kernel<<<grid, kLossThreads, 0, st>>>(logits_dev, y_dev, batch, loss_dev, dlogits_dev,
+                                                      reinterpret_cast<unsigned long long*>(step_counter_dev), scr);
   B200_LAUNCH_CHECK();
   return B200DS_OK;
 }

@@ -102,6 +102,19 @@ B200DS_API int b200ds_bce_loss_grad(const float* logits_dev, const float* y_dev,
                          float* loss_dev, float* dlogits_dev, uint64_t* step_counter_dev,
                          void* scratch_dev, size_t scratch_bytes, uintptr_t stream);
 
+/* The same pass without any scratch argument.  No counterpart in the reference: it exists for
+ * hosts of this ABI that cannot allocate device memory themselves -- a launcher that only
+ * holds the buffers its framework gave it, or a step loop under a caching allocator that
+ * already owns the GPU, where a stray cudaMalloc may fail or stall the step.  The scratch is a
+ * 1280-byte array built into the library (present on every GPU that loads it); nothing is
+ * allocated or freed.  Limit: batch <= 4194304 rows, larger batches are rejected
+ * (B200DS_ERR_ARG) -- use b200ds_bce_loss_grad for those.  The first call on a device looks the
+ * array's address up and should be made outside stream capture.  All calls share the array:
+ * calls whose GPU work may overlap must be ordered by the caller. */
+B200DS_API int b200ds_bce_loss_grad_noalloc(const float* logits_dev, const float* y_dev, int64_t batch,
+                                            float* loss_dev, float* dlogits_dev,
+                                            uint64_t* step_counter_dev, uintptr_t stream);
+
 /* model_engine.backward(loss) up to the all-reduce (train.py:113): recomputes the hidden
  * activation, writes dW1, db1, dW2, db2 into grads_dev (flat layout, overwritten).
  * No dx is formed (the input does not require grad).  F <= 256 on this path. */
