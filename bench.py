@@ -198,24 +198,29 @@ class WideStep:
         self.seed = SEED + 1000003 * rank           # distinct Philox key per rank
         self.offset = 0
         self.tc = precision == "bf16"
+        self.primed = False
         if self.tc:
             assert lib.b200ds_tc_supported(B, F, H), "bf16 tensor-core path does not take this shape"
             self.xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=dev)
             self.wq = torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=dev)
             self.bwd_sc = torch.zeros(max(256, lib.b200ds_mlp_backward_tc_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
             self.dominant = dict(name="mlp_bwd_tc_kernel", bound="tensor")
-        # philox, label, [pack_x, pack_w1], forward, loss, backward, finish, adam
-        self.launches_per_step = 9 if self.tc else 7
+        # bf16: gen_batch, pack_w1, forward, loss, backward, finish, adam; fp32: philox, label, forward, loss, backward, finish, adam
+        self.launches_per_step = 7
 
     def step(self, st, ev_pair=None):
         lib, chk = self.lib, self._lib.check
         B, F, H = self.B, self.F, self.H
         # the draw index is the device step counter (incremented by the loss kernel), so the same
         # launch sequence can be replayed from a CUDA graph and still get a fresh batch each step
-        chk(lib.b200ds_philox_normal_counted(self.x.data_ptr(), B * F, self.seed, 0, self.counter.data_ptr(), st))
-        chk(lib.b200ds_label_rule(self.x.data_ptr(), self.y.data_ptr(), B, F, st))
         if self.tc:
-            chk(lib.b200ds_pack_x_bf16(self.x.data_ptr(), B, F, self.xq.data_ptr(), st))
+            if not self.primed:      # batch 0; later batches are drawn beside the previous step's all-reduce
+                self.gen_next(st)
+                self.primed = True
+        else:
+            chk(lib.b200ds_philox_normal_counted(self.x.data_ptr(), B * F, self.seed, 0, self.counter.data_ptr(), st))
+            chk(lib.b200ds_label_rule(self.x.data_ptr(), self.y.data_ptr(), B, F, st))
+        if self.tc:
             chk(lib.b200ds_pack_params_bf16(self.params.data_ptr(), F, H, self.wq.data_ptr(), st))
             chk(lib.b200ds_mlp_forward_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.params.data_ptr(), B, F, H,
                                           self.logits.data_ptr(), st))
@@ -233,10 +238,23 @@ class WideStep:
                                             self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
         if ev_pair:
             ev_pair[1].record()
-        chk(lib.b200ds_allreduce_bucket(self.ctx, self.grads.data_ptr(), self.P, st))
+        if self.tc:
+            # the next batch does not need this step's gradients: it is generated on the main stream
+            # while the all-reduce runs on the context's side stream (the backward is done with xq)
+            chk(lib.b200ds_allreduce_bucket_begin(self.ctx, self.grads.data_ptr(), self.P, st))
+            self.gen_next(st)
+            chk(lib.b200ds_allreduce_bucket_end(self.ctx, st))
+        else:
+            chk(lib.b200ds_allreduce_bucket(self.ctx, self.grads.data_ptr(), self.P, st))
         chk(lib.b200ds_adam_step_counted(self.params.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
                                          self.Ppad, LR, 0.9, 0.999, 1e-8, self.counter.data_ptr(),
                                          1.0 / self.world, 0, st))
+
+    def gen_next(self, st):
+        """Batch number *counter of the Philox stream (the loss kernel has already counted this
+        step), drawn straight into the bf16 pack together with its labels."""
+        self._lib.check(self.lib.b200ds_gen_batch_bf16_counted(self.xq.data_ptr(), self.y.data_ptr(), self.B, self.F,
+                                                               self.seed, 0, self.counter.data_ptr(), st))
 
     dominant = dict(name="mlp_backward_f32_kernel (+finish)", bound="tensor")   # overridden per instance for bf16
 
@@ -308,7 +326,8 @@ def run_ours(a):
         clk.start()
         wall0 = time.perf_counter()
         for i in range(K):
-            flush.fill_(i & 0xFF)                 # L2 flush between timed steps, outside the event bracket
+            if not os.environ.get("B200DS_BENCH_NOFLUSH"):
+                flush.fill_(i & 0xFF)             # L2 flush between timed steps, outside the event bracket
             evs[i][0].record()
             graph.replay()
             evs[i][1].record()

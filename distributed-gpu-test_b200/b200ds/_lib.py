@@ -51,6 +51,8 @@ PROTOTYPES = {
     "b200ds_mlp_backward_f32_scratch_bytes": (C.c_size_t, [c_i64, C.c_int, C.c_int]),
     "b200ds_mlp_backward_f32": (C.c_int, [c_ptr, c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_ptr, C.c_size_t, c_stream]),
     "b200ds_allreduce_bucket": (C.c_int, [c_ptr, c_ptr, c_i64, c_stream]),
+    "b200ds_allreduce_bucket_begin": (C.c_int, [c_ptr, c_ptr, c_i64, c_stream]),
+    "b200ds_allreduce_bucket_end": (C.c_int, [c_ptr, c_stream]),
     "b200ds_broadcast_params": (C.c_int, [c_ptr, c_ptr, c_i64, c_stream]),
     "b200ds_barrier": (C.c_int, [c_ptr]),
     "b200ds_adam_step": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, C.c_double, C.c_double, C.c_double,
@@ -64,6 +66,8 @@ PROTOTYPES = {
     "b200ds_tc_xq_bytes": (C.c_size_t, [c_i64]),
     "b200ds_tc_wq_bytes": (C.c_size_t, [C.c_int]),
     "b200ds_pack_x_bf16": (C.c_int, [c_ptr, c_i64, C.c_int, c_ptr, c_stream]),
+    "b200ds_gen_batch_bf16": (C.c_int, [c_ptr, c_ptr, c_i64, C.c_int, c_u64, c_u64, C.POINTER(c_u64), c_stream]),
+    "b200ds_gen_batch_bf16_counted": (C.c_int, [c_ptr, c_ptr, c_i64, C.c_int, c_u64, c_u64, c_ptr, c_stream]),
     "b200ds_pack_params_bf16": (C.c_int, [c_ptr, C.c_int, C.c_int, c_ptr, c_stream]),
     "b200ds_mlp_forward_tc": (C.c_int, [c_ptr, c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_stream]),
     "b200ds_mlp_backward_tc_scratch_bytes": (C.c_size_t, [c_i64, C.c_int, C.c_int]),

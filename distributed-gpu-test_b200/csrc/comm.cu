@@ -137,7 +137,7 @@ int b200ds_ctx_info(const b200ds_ctx* ctx, int* device, int* rank, int* world) {
   return B200DS_OK;
 }
 
-int b200ds_allreduce_bucket(b200ds_ctx* ctx, float* bucket_dev, int64_t n, uintptr_t stream) {
+int b200ds_allreduce_bucket_begin(b200ds_ctx* ctx, float* bucket_dev, int64_t n, uintptr_t stream) {
   B200_REQUIRE(ctx != nullptr, "allreduce_bucket: null context");
   B200_REQUIRE(n >= 0, "allreduce_bucket: negative n");
   if (ctx->world == 1 || n == 0) return B200DS_OK;
@@ -150,8 +150,21 @@ int b200ds_allreduce_bucket(b200ds_ctx* ctx, float* bucket_dev, int64_t n, uintp
   B200_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_ready, 0));
   B200_NCCL(api, api->AllReduce(bucket_dev, bucket_dev, (size_t)n, ncclFloat32, ncclSum, ctx->comm, ctx->side));
   B200_CUDA(cudaEventRecord(ctx->ev_done, ctx->side));
-  B200_CUDA(cudaStreamWaitEvent(s, ctx->ev_done, 0));
   return B200DS_OK;
+}
+
+int b200ds_allreduce_bucket_end(b200ds_ctx* ctx, uintptr_t stream) {
+  B200_REQUIRE(ctx != nullptr, "allreduce_bucket_end: null context");
+  if (ctx->world == 1) return B200DS_OK;
+  B200_CUDA(cudaStreamWaitEvent(as_stream(stream), ctx->ev_done, 0));
+  return B200DS_OK;
+}
+
+int b200ds_allreduce_bucket(b200ds_ctx* ctx, float* bucket_dev, int64_t n, uintptr_t stream) {
+  int rc = b200ds_allreduce_bucket_begin(ctx, bucket_dev, n, stream);
+  if (rc) return rc;
+  if (n == 0) return B200DS_OK;
+  return b200ds_allreduce_bucket_end(ctx, stream);
 }
 
 int b200ds_broadcast_params(b200ds_ctx* ctx, float* params_dev, int64_t n, uintptr_t stream) {

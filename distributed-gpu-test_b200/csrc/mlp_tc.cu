@@ -24,6 +24,7 @@
 //                 dW2[n]  = sum_k w1q[n,k] S[n,k]  (= sum_b dz[b] h[b,n]),  db2 = sum_b dz[b].
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "philox.cuh"
 
 namespace b200ds {
 using namespace tc;
@@ -56,6 +57,54 @@ pack_x_kernel(const float* __restrict__ x, int64_t batch, int F, uint4* __restri
     v[j] = __float2bfloat16(f);
   }
   xq[t] = *reinterpret_cast<uint4*>(v);
+}
+
+// Generated batch straight into the tensor-core pack (BASELINE config 4: the batch is drawn on
+// the device every step).  Element (row, k) is element li = row*F + k of
+// torch.randn(B*F, device='cuda') under (seed, offset): Philox counter offset/4 + li/(4*nthreads),
+// subsequence li % nthreads, output (li / nthreads) % 4 -- the mapping of philox_normal_kernel.
+// One thread = one 16-byte chunk of xq (same thread->address map as pack_x_kernel); the label
+// rule (train.py:22-23) is evaluated on the fp32 values in the order label_rule_kernel uses,
+// the values of the second chunk arriving by shuffle.  fp32 x is never written.
+template <typename idx_t>      // uint32_t when batch*F < 2^31 (64-bit div/mod would dominate the kernel)
+__global__ void __launch_bounds__(256)
+gen_batch_kernel(uint4* __restrict__ xq, float* __restrict__ y, int64_t batch, int F, uint2 key, uint64_t ctr0,
+                 int64_t nthreads, int calls, const unsigned long long* __restrict__ draw_counter) {
+  if (draw_counter) ctr0 += (uint64_t)(*draw_counter) * (uint64_t)calls;
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;      // batch % 8 == 0: whole warps only
+  const int r8 = (int)(t & 7), c = (int)((t >> 3) & 3);
+  const int64_t row = ((t >> 5) << 3) + r8;
+  float v[8];
+  __nv_bfloat16 q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int k = c * 8 + j;
+    float f = k < F + 2 ? 1.f : 0.f;
+    if (k < F) {
+      const idx_t li = (idx_t)row * (idx_t)F + (idx_t)k;
+      const idx_t tt = li / (idx_t)nthreads;
+      const idx_t sub = li - tt * (idx_t)nthreads;
+      const uint64_t ctr = ctr0 + (uint64_t)(tt >> 2);
+      const uint4 r = philox4x32_10(make_uint4((unsigned)ctr, (unsigned)(ctr >> 32), (unsigned)sub, (unsigned)((uint64_t)sub >> 32)), key);
+      const float2 p = (tt & 2) ? box_muller(r.z, r.w) : box_muller(r.x, r.y);
+      f = (tt & 1) ? p.y : p.x;
+    }
+    v[j] = f;
+    q[j] = __float2bfloat16(f);
+  }
+  xq[t] = *reinterpret_cast<uint4*>(q);
+  // label: sum of columns 0 .. F/2-1 in index order (F/2 <= 15: chunk 0 and part of chunk 1)
+  float acc = 0.f;
+  const int half = F >> 1;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (j < half) acc += v[j];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float nxt = __shfl_down_sync(0xffffffffu, v[j], 8);     // column 8 + j of the same row
+    if (8 + j < half) acc += nxt;
+  }
+  if (c == 0) y[row] = acc > 0.f ? 1.f : 0.f;
 }
 
 constexpr int kPackRows = 64;             // rows of W1 per pack_w1 block (256 threads = 64 rows x 4 k chunks)
@@ -201,16 +250,12 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
           const uint32_t rph = (uint32_t)(q / kFwdRing) & 1u;
           const uint64_t wd = wdesc0 + (uint64_t)((c * kTileBytes) >> 4);
           const uint32_t dcol = tmem + r * 128;
-#if !defined(B200DS_ABLATE) || B200DS_ABLATE < 3
           mbar_wait(&sh->d1_free[r], rph ^ 1);
-#endif
           tc_fence_after();
           if (elect_one()) {
             mma_ss(dcol, wd, xd, idesc, 0);
             mma_ss(dcol, wd + (2 * LBO_K >> 4), xd + (2 * LBO_K >> 4), idesc, 1);
-#if !defined(B200DS_ABLATE) || B200DS_ABLATE < 4
             mma_commit(&sh->d1_full[r]);
-#endif
           }
           __syncwarp();
         }
@@ -610,6 +655,41 @@ int b200ds_pack_x_bf16(const float* x_dev, int64_t batch, int n_features, void* 
   pack_x_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, as_stream(stream)>>>(x_dev, batch, n_features, reinterpret_cast<uint4*>(xq_dev));
   B200_LAUNCH_CHECK();
   return B200DS_OK;
+}
+
+static int launch_gen_batch(void* xq_dev, float* y_dev, int64_t batch, int n_features, uint64_t seed, uint64_t offset,
+                            const uint64_t* draw_counter_dev, uint64_t* offset_advance, uintptr_t stream) {
+  B200_REQUIRE(batch > 0 && batch % 8 == 0, "gen_batch_bf16: batch must be a positive multiple of 8 (got %lld)", (long long)batch);
+  B200_REQUIRE(n_features >= 1 && n_features + 2 <= KP, "gen_batch_bf16: F must be in [1,%d] (got %d)", KP - 2, n_features);
+  B200_REQUIRE(offset % 4 == 0, "gen_batch_bf16: offset must be a multiple of 4");
+  B200_REQUIRE(xq_dev && y_dev, "gen_batch_bf16: null pointer");
+  int grid, calls;
+  philox_plan(batch * n_features, &grid, &calls);
+  int64_t threads = batch * (KP / 8);
+  const unsigned blocks = (unsigned)((threads + 255) / 256);
+  const uint2 key = make_uint2((unsigned)seed, (unsigned)(seed >> 32));
+  if (batch * n_features < (int64_t)1 << 31)
+    gen_batch_kernel<uint32_t><<<blocks, 256, 0, as_stream(stream)>>>(
+        reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256, calls,
+        reinterpret_cast<const unsigned long long*>(draw_counter_dev));
+  else
+    gen_batch_kernel<uint64_t><<<blocks, 256, 0, as_stream(stream)>>>(
+        reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256, calls,
+        reinterpret_cast<const unsigned long long*>(draw_counter_dev));
+  B200_LAUNCH_CHECK();
+  if (offset_advance) *offset_advance = (uint64_t)calls * 4;
+  return B200DS_OK;
+}
+
+int b200ds_gen_batch_bf16(void* xq_dev, float* y_dev, int64_t batch, int n_features, uint64_t seed, uint64_t offset,
+                          uint64_t* offset_advance, uintptr_t stream) {
+  return launch_gen_batch(xq_dev, y_dev, batch, n_features, seed, offset, nullptr, offset_advance, stream);
+}
+
+int b200ds_gen_batch_bf16_counted(void* xq_dev, float* y_dev, int64_t batch, int n_features, uint64_t seed,
+                                  uint64_t offset0, const uint64_t* draw_counter_dev, uintptr_t stream) {
+  B200_REQUIRE(draw_counter_dev != nullptr, "gen_batch_bf16_counted: null draw counter");
+  return launch_gen_batch(xq_dev, y_dev, batch, n_features, seed, offset0, draw_counter_dev, nullptr, stream);
 }
 
 int b200ds_pack_params_bf16(const float* params_dev, int n_features, int hidden, void* wq_dev, uintptr_t stream) {

@@ -10,38 +10,9 @@
 // output element sees.  Do NOT build this file with --use_fast_math or -fmad=false: the
 // bit pattern of logf and the FMA contraction below are part of the contract.
 #include "common.cuh"
+#include "philox.cuh"
 
 namespace b200ds {
-
-__device__ __forceinline__ uint4 philox_round(uint4 c, uint2 k) {
-  const unsigned M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
-  unsigned hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
-  unsigned hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
-  return make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
-}
-
-__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
-#pragma unroll
-  for (int r = 0; r < 9; ++r) {
-    c = philox_round(c, k);
-    k.x += 0x9E3779B9u;
-    k.y += 0xBB67AE85u;
-  }
-  return philox_round(c, k);
-}
-
-__device__ __forceinline__ float2 box_muller(unsigned a, unsigned b) {
-  const float inv = 2.3283064e-10f;                   // 2^-32
-  const float inv2pi = 2.3283064e-10f * 6.2831855f;   // 2^-32 * 2pi
-  float u = a * inv + (inv / 2);
-  float v = b * inv2pi + (inv2pi / 2);
-  float s = sqrtf(-2.0f * logf(u));
-  float2 r;
-  __sincosf(v, &r.x, &r.y);
-  r.x *= s;
-  r.y *= s;
-  return r;
-}
 
 // One thread = one Philox subsequence, exactly as ATen launches it.
 __global__ void __launch_bounds__(256) philox_normal_kernel(float* __restrict__ out, int64_t numel,

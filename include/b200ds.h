@@ -130,6 +130,12 @@ B200DS_API int b200ds_mlp_backward_f32(const float* params_dev, const float* x_d
  * caller's ordering is preserved without a host sync.  The 1/world scale is NOT applied
  * here; pass grad_scale = 1/world to b200ds_adam_step.  world == 1: no-op. */
 B200DS_API int b200ds_allreduce_bucket(b200ds_ctx* ctx, float* bucket_dev, int64_t n, uintptr_t stream);
+/* The same exchange in two halves, so that work which does not need the gradients (the next
+ * batch's generation, say) can be enqueued on `stream` between them and run beside the
+ * all-reduce: _begin orders the side stream after `stream` and starts the all-reduce, _end
+ * makes `stream` wait for it.  One exchange in flight per context. */
+B200DS_API int b200ds_allreduce_bucket_begin(b200ds_ctx* ctx, float* bucket_dev, int64_t n, uintptr_t stream);
+B200DS_API int b200ds_allreduce_bucket_end(b200ds_ctx* ctx, uintptr_t stream);
 /* Parameter broadcast from rank 0 done by deepspeed.initialize (train.py:87-93). */
 B200DS_API int b200ds_broadcast_params(b200ds_ctx* ctx, float* params_dev, int64_t n, uintptr_t stream);
 /* dist.barrier() at teardown (train.py:134): host-blocking. */
@@ -188,6 +194,18 @@ B200DS_API size_t b200ds_tc_xq_bytes(int64_t batch);
 B200DS_API size_t b200ds_tc_wq_bytes(int hidden);
 B200DS_API int b200ds_pack_x_bf16(const float* x_dev, int64_t batch, int n_features, void* xq_dev,
                                   uintptr_t stream);
+/* Generated-batch configs: draw the batch and write it straight into the pack, with its
+ * labels -- xq[b,k] = bf16(x[b,k]) where x = torch.randn(batch*F, device='cuda') under
+ * (seed, offset) viewed as [batch,F] (same stream and mapping as b200ds_philox_normal), and
+ * y[b] by the rule of train.py:22-23 on the fp32 values.  Replaces b200ds_philox_normal +
+ * b200ds_label_rule + b200ds_pack_x_bf16 by one launch; fp32 x is never materialised.
+ * The _counted form takes the draw index from a device counter (CUDA-graph replay). */
+B200DS_API int b200ds_gen_batch_bf16(void* xq_dev, float* y_dev, int64_t batch, int n_features,
+                                     uint64_t seed, uint64_t offset, uint64_t* offset_advance,
+                                     uintptr_t stream);
+B200DS_API int b200ds_gen_batch_bf16_counted(void* xq_dev, float* y_dev, int64_t batch, int n_features,
+                                             uint64_t seed, uint64_t offset0,
+                                             const uint64_t* draw_counter_dev, uintptr_t stream);
 B200DS_API int b200ds_pack_params_bf16(const float* params_dev, int n_features, int hidden, void* wq_dev,
                                        uintptr_t stream);
 /* model_engine(batch_x) (train.py:107): logits[b] = relu(xq[b,:] . w1q[n,:]) . W2 + b2, the

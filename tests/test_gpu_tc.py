@@ -179,3 +179,43 @@ def test_host_buffer_step_tc_path(lib, cuda_dev):
         assert abs(float(lh) - float(lref)) <= 2e-2 * abs(float(lref)), step
     assert float((params[:P].cpu() - flat).abs().max()) <= 2e-2 * float(flat.abs().max())
     _chk(lib.b200ds_ctx_destroy(ctx))
+
+
+@pytest.mark.parametrize("B,F", [(128, 20), (65536, 20), (1024, 30), (256, 1), (4096, 7)])
+def test_fused_batch_generator_is_bit_identical_to_the_three_kernel_path(lib, cuda_dev, B, F):
+    """b200ds_gen_batch_bf16 == philox_normal -> label_rule -> pack_x, byte for byte, also at a
+    later offset and through the device draw counter."""
+    seed = 42 + B
+    x = torch.empty(B * F, device=cuda_dev)
+    y_ref = torch.empty(B, device=cuda_dev)
+    xq_ref = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=cuda_dev)
+    xq = torch.empty_like(xq_ref)
+    y = torch.empty(B, device=cuda_dev)
+    adv = C.c_uint64(0)
+    off = 0
+    ctr = torch.zeros(1, dtype=torch.int64, device=cuda_dev)
+    for draw in range(3):
+        _chk(lib.b200ds_philox_normal(x.data_ptr(), B * F, seed, off, C.byref(adv), _st()))
+        _chk(lib.b200ds_label_rule(x.data_ptr(), y_ref.data_ptr(), B, F, _st()))
+        _chk(lib.b200ds_pack_x_bf16(x.data_ptr(), B, F, xq_ref.data_ptr(), _st()))
+        xq.zero_(); y.fill_(-1)
+        adv2 = C.c_uint64(0)
+        if draw < 2:
+            _chk(lib.b200ds_gen_batch_bf16(xq.data_ptr(), y.data_ptr(), B, F, seed, off, C.byref(adv2), _st()))
+            assert adv2.value == adv.value
+        else:
+            ctr.fill_(draw)
+            _chk(lib.b200ds_gen_batch_bf16_counted(xq.data_ptr(), y.data_ptr(), B, F, seed, 0, ctr.data_ptr(), _st()))
+        torch.cuda.synchronize()
+        assert torch.equal(xq, xq_ref), (B, F, draw)
+        assert torch.equal(y, y_ref), (B, F, draw)
+        off += adv.value
+    # and the fp32 values underneath are torch's own CUDA generator stream
+    g = torch.Generator(device=cuda_dev); g.manual_seed(seed)
+    assert torch.equal(torch.randn(B * F, device=cuda_dev, generator=g), _first_draw(lib, cuda_dev, B * F, seed))
+
+
+def _first_draw(lib, dev, n, seed):
+    out = torch.empty(n, device=dev)
+    _chk(lib.b200ds_philox_normal(out.data_ptr(), n, seed, 0, None, _st()))
+    return out
