@@ -18,7 +18,8 @@
 //           the first sum is linear in x (= xq[b,:] . v, v = w1q^T w2, 32 numbers per slice),
 //           the second is ONE FFMA with an |.| source modifier per accumulator element.
 // backward  per (128 n block, 128-row b tile):  D1T = w1q_block . xq_tile^T   (SS MMA, recompute)
-//           epilogue: A2[n,b] = 1[z1>0] * dz[b] as bf16, written back IN PLACE into TMEM,
+//           epilogue: A2[n,b] = 1[z1 not negative] * dz[b] as bf16 (sign-bit test, 2 instructions per
+//           pair; it differs from relu'(z1) only for z1 == +0.0 exactly), written back IN PLACE into TMEM,
 //           S[n,k] += A2 . xq_tile   (TS MMA, A from TMEM, B = the same x tile read MN-major)
 //           then  dW1[n,f] = w2[n] S[n,f],  db1[n] = w2[n] S[n,F],
 //                 dW2[n]  = sum_k w1q[n,k] S[n,k]  (= sum_b dz[b] h[b,n]),  db2 = sum_b dz[b].
@@ -509,10 +510,9 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
             const uint32_t dd[4] = {d4[c4].x, d4[c4].y, d4[c4].z, d4[c4].w};                       \
             _Pragma("unroll") for (int e = 0; e < 4; ++e) {                                       \
               const int c = c4 * 4 + e;                                                            \
-              uint32_t h = pack_relu_bf16x2(__uint_as_float(CUR[2 * c]), __uint_as_float(CUR[2 * c + 1])); \
-              uint32_t m;                                                                          \
-              asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(m) : "r"(h), "r"(0u));                    \
-              p[c] = m & dd[e];                                                                    \
+              uint32_t neg;   /* 0xFFFF in a half whose z1 has the sign bit set (byte-permute with sign replication) */ \
+              asm("prmt.b32 %0, %1, %2, 0xFFBB;" : "=r"(neg) : "r"(CUR[2 * c]), "r"(CUR[2 * c + 1]));      \
+              p[c] = dd[e] & ~neg;                                                                 \
             }                                                                                      \
           }                                                                                        \
           tmem_st16(tbase + (J) * 16, p);                                                          \
