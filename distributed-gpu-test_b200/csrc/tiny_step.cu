@@ -29,21 +29,29 @@ struct TinyArgs {
   const float* x_all; const float* y_all; const int64_t* order;
   int64_t n_order, first;
   int F, H, batch, n_steps, apply_adam;
-  double lr, beta1, beta2, b1pow0, b2pow0;   // b?pow0 = beta^step0
+  double lr, beta1, beta2;
+  long long step0;                           // Adam t before the first step of this launch
   float w1, beta2f, w2, eps;                 // (float)(1-beta1), (float)beta2, (float)(1-beta2), (float)eps
   float* losses;
 };
 
+// Adam for a register-resident parameter.  This kernel is latency-bound (one CTA, a few
+// hundred dependent instructions per step), so the two divisions and the square root of the
+// update use the hardware approximations (sqrt.approx / rcp, <= 2 ulp each) instead of the
+// IEEE sequences adam.cu uses; the difference is ~1e-7 relative per update, two orders of
+// magnitude inside the 1e-5 parity tolerance.  inv_bc2_sqrt = 1/sqrt(1 - beta2^t).
 __device__ __forceinline__ void adam_reg(float& p, float g, float& m, float& v, const TinyArgs& a,
-                                         float neg_step, float bc2_sqrt) {
+                                         float neg_step, float inv_bc2_sqrt) {
   m = fmaf(a.w1, g - m, m);
-  v = v * a.beta2f;
-  v = fmaf(a.w2 * g, g, v);
-  float denom = sqrtf(v) / bc2_sqrt + a.eps;
-  p = fmaf(neg_step, m / denom, p);
+  v = fmaf(a.w2 * g, g, v * a.beta2f);
+  float sq;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(v));
+  const float denom = fmaf(sq, inv_bc2_sqrt, a.eps);
+  p = fmaf(neg_step, __fdividef(m, denom), p);
 }
 
-template <int FP>
+// BT: compile-time bound on the per-step batch (row loops fully unrolled and interleaved)
+template <int FP, int BT>
 __global__ void __launch_bounds__(kTinyMaxHidden, 1) tiny_train_steps_kernel(TinyArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
@@ -55,8 +63,8 @@ __global__ void __launch_bounds__(kTinyMaxHidden, 1) tiny_train_steps_kernel(Tin
   float* zpart = hs + B * HP;                                 // [B][nwarp]
   float* dzs = zpart + B * nwarp;                             // [B]
   float* terms = dzs + B;                                     // [B]
-  float* sc = terms + B;                                      // [2][2] adam scalars, by step parity
-  int* ord = reinterpret_cast<int*>(sc + 4);                  // [n_steps*B]
+  float* sc = terms + B;                                      // [n_steps][2] adam scalars (-lr/bc1, 1/sqrt(bc2)) per step
+  int* ord = reinterpret_cast<int*>(sc + 2 * a.n_steps);      // [n_steps*B]
 
   const Layout L{F, H};
   const bool own = tid < H;
@@ -84,6 +92,15 @@ __global__ void __launch_bounds__(kTinyMaxHidden, 1) tiny_train_steps_kernel(Tin
   const int total = (int)min((int64_t)a.n_steps * B, avail);
   for (int i = tid; i < total; i += blockDim.x) ord[i] = (int)a.order[a.first + i];
   for (int i = tid; i < 2 * B * FP; i += blockDim.x) xs[i] = 0.f;   // zero the K padding once
+  if (a.apply_adam) {
+    // bias corrections of every step of this launch, formed in double exactly as torch does
+    // (1 - beta ** t), in parallel and off the per-step critical path
+    for (int i = tid; i < a.n_steps; i += blockDim.x) {
+      const double t = (double)(a.step0 + i + 1);
+      sc[2 * i + 0] = (float)(-(a.lr / (1.0 - pow(a.beta1, t))));
+      sc[2 * i + 1] = (float)(1.0 / sqrt(1.0 - pow(a.beta2, t)));
+    }
+  }
   __syncthreads();
 
   auto prefetch = [&](int s) {   // rows of step s -> buffer s&1
@@ -99,18 +116,11 @@ __global__ void __launch_bounds__(kTinyMaxHidden, 1) tiny_train_steps_kernel(Tin
     cp_async_commit();
   };
 
-  double b1pow = a.b1pow0, b2pow = a.b2pow0;
   if (total > 0) prefetch(0);
   for (int s = 0; s < a.n_steps; ++s) {
     const int pos = s * B;
     const int nb = min(B, total - pos);
     if (nb <= 0) break;
-    if (tid == 0 && a.apply_adam) {
-      b1pow *= a.beta1;
-      b2pow *= a.beta2;
-      sc[(s & 1) * 2 + 0] = (float)(-(a.lr / (1.0 - b1pow)));
-      sc[(s & 1) * 2 + 1] = (float)sqrt(1.0 - b2pow);
-    }
     cp_async_wait_all();
     __syncthreads();                       // S1: step s rows landed; everyone is done with step s-1
     if (s + 1 < a.n_steps && pos + B < total) prefetch(s + 1);
@@ -118,30 +128,51 @@ __global__ void __launch_bounds__(kTinyMaxHidden, 1) tiny_train_steps_kernel(Tin
     const float* yb = ys + (s & 1) * B;
 
     // ---- forward: z1 = b1 + x . W1[n,:], h = relu(z1), partial of h . w2
-    for (int r = 0; r < nb; ++r) {
-      const float4* xr = reinterpret_cast<const float4*>(xb + r * FP);
-      float z1 = b1;
+    {
+      float hrow[BT], pz[BT];
 #pragma unroll
-      for (int q = 0; q < FP / 4; ++q) {
-        float4 xv = xr[q];
-        z1 = fmaf(xv.x, w[4 * q + 0], z1);
-        z1 = fmaf(xv.y, w[4 * q + 1], z1);
-        z1 = fmaf(xv.z, w[4 * q + 2], z1);
-        z1 = fmaf(xv.w, w[4 * q + 3], z1);
+      for (int r = 0; r < BT; ++r) {
+        float z1 = b1;
+        if (r < nb) {
+          const float4* xr = reinterpret_cast<const float4*>(xb + r * FP);
+#pragma unroll
+          for (int q = 0; q < FP / 4; ++q) {
+            float4 xv = xr[q];
+            z1 = fmaf(xv.x, w[4 * q + 0], z1);
+            z1 = fmaf(xv.y, w[4 * q + 1], z1);
+            z1 = fmaf(xv.z, w[4 * q + 2], z1);
+            z1 = fmaf(xv.w, w[4 * q + 3], z1);
+          }
+        }
+        hrow[r] = (own && r < nb) ? fmaxf(z1, 0.f) : 0.f;
+        pz[r] = hrow[r] * w2;
       }
-      float h = own ? fmaxf(z1, 0.f) : 0.f;
-      hs[r * HP + tid] = h;
-      float pz = warp_sum(h * w2);
-      if (lane == 0) zpart[r * nwarp + warp] = pz;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < BT; ++r) pz[r] += __shfl_xor_sync(0xffffffffu, pz[r], o);
+      }
+#pragma unroll
+      for (int r = 0; r < BT; ++r) {
+        if (r < nb) {
+          hs[r * HP + tid] = hrow[r];
+          if (lane == 0) zpart[r * nwarp + warp] = pz[r];
+        }
+      }
     }
     __syncthreads();                       // S2
-    if (tid < nb) {
-      float z = 0.f;
-      for (int q = 0; q < nwarp; ++q) z += zpart[tid * nwarp + q];
-      z += b2;
-      float y = yb[tid];
-      terms[tid] = bce_term(z, y);
-      dzs[tid] = bce_grad(z, y, (float)nb);
+    {   // loss term and its derivative of row r are formed by two different warps side by side
+      const bool second = nwarp > 1;
+      const int r = second ? (tid & 31) : tid;
+      const bool do_term = tid < nb, do_grad = second ? (warp == 1 && r < nb) : (tid < nb);
+      if (do_term || do_grad) {
+        float z = 0.f;
+        for (int q = 0; q < nwarp; ++q) z += zpart[r * nwarp + q];
+        z += b2;
+        const float y = yb[r];
+        if (do_term) terms[r] = bce_term(z, y);
+        if (do_grad) dzs[r] = bce_grad(z, y, (float)nb);
+      }
     }
     __syncthreads();                       // S3
     if (tid == 0) {
@@ -155,7 +186,9 @@ __global__ void __launch_bounds__(kTinyMaxHidden, 1) tiny_train_steps_kernel(Tin
 #pragma unroll
     for (int f = 0; f < FP; ++f) gw[f] = 0.f;
     float gb1 = 0.f, gw2 = 0.f, gb2 = 0.f;
-    for (int r = 0; r < nb; ++r) {
+#pragma unroll
+    for (int r = 0; r < BT; ++r) {
+      if (r >= nb) break;
       float d = dzs[r];
       float h = hs[r * HP + tid];
       float gz = h > 0.f ? d * w2 : 0.f;
@@ -174,16 +207,26 @@ __global__ void __launch_bounds__(kTinyMaxHidden, 1) tiny_train_steps_kernel(Tin
     }
 
     if (a.apply_adam) {
-      const float neg_step = sc[(s & 1) * 2 + 0], bc2_sqrt = sc[(s & 1) * 2 + 1];
-      if (own) {
+      const float neg_step = sc[2 * s + 0], inv_bc2 = sc[2 * s + 1];
+      // Unpredicated and staged: padding columns and threads beyond H hold zeros everywhere
+      // (g = m = v = 0 leaves p untouched), so every thread runs the same straight-line code and
+      // the FP + 3 independent updates overlap their sqrt / reciprocal latencies.
+      float sq[FP], qd[FP];
 #pragma unroll
-        for (int f = 0; f < FP; ++f)
-          if (f < F) adam_reg(w[f], gw[f], mw[f], vw[f], a, neg_step, bc2_sqrt);
-        adam_reg(b1, gb1, mb1, vb1, a, neg_step, bc2_sqrt);
-        adam_reg(w2, gw2, mw2, vw2, a, neg_step, bc2_sqrt);
+      for (int f = 0; f < FP; ++f) {
+        mw[f] = fmaf(a.w1, gw[f] - mw[f], mw[f]);
+        vw[f] = fmaf(a.w2 * gw[f], gw[f], vw[f] * a.beta2f);
       }
+#pragma unroll
+      for (int f = 0; f < FP; ++f) asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq[f]) : "f"(vw[f]));
+#pragma unroll
+      for (int f = 0; f < FP; ++f) qd[f] = __fdividef(mw[f], fmaf(sq[f], inv_bc2, a.eps));
+#pragma unroll
+      for (int f = 0; f < FP; ++f) w[f] = fmaf(neg_step, qd[f], w[f]);
+      adam_reg(b1, gb1, mb1, vb1, a, neg_step, inv_bc2);
+      adam_reg(w2, gw2, mw2, vw2, a, neg_step, inv_bc2);
       // every thread tracks b2 identically (it is needed by the threads that form z)
-      adam_reg(b2, gb2, mb2, vb2, a, neg_step, bc2_sqrt);
+      adam_reg(b2, gb2, mb2, vb2, a, neg_step, inv_bc2);
     } else {
       if (own) {
 #pragma unroll
@@ -212,19 +255,26 @@ __global__ void __launch_bounds__(kTinyMaxHidden, 1) tiny_train_steps_kernel(Tin
   }
 }
 
-template <int FP>
-static int launch_tiny(const TinyArgs& a, cudaStream_t st) {
+template <int FP, int BT>
+static int launch_tiny_bt(const TinyArgs& a, cudaStream_t st) {
   int threads = (a.H + 31) / 32 * 32;
   int nwarp = threads / 32;
   int total = (int)((int64_t)a.n_steps * a.batch);
   size_t smem = sizeof(float) * ((size_t)2 * a.batch * FP + 2 * a.batch + (size_t)a.batch * threads +
-                                 (size_t)a.batch * nwarp + 2 * a.batch + 4) + sizeof(int) * (size_t)total;
+                                 (size_t)a.batch * nwarp + 2 * a.batch + 2 * (size_t)a.n_steps) + sizeof(int) * (size_t)total;
   smem = (smem + 15) / 16 * 16;
   if (smem > 48 * 1024)
-    B200_CUDA(cudaFuncSetAttribute(tiny_train_steps_kernel<FP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  tiny_train_steps_kernel<FP><<<1, threads, smem, st>>>(a);
+    B200_CUDA(cudaFuncSetAttribute(tiny_train_steps_kernel<FP, BT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  tiny_train_steps_kernel<FP, BT><<<1, threads, smem, st>>>(a);
   B200_LAUNCH_CHECK();
   return B200DS_OK;
+}
+
+template <int FP>
+static int launch_tiny(const TinyArgs& a, cudaStream_t st) {
+  if (a.batch <= 4) return launch_tiny_bt<FP, 4>(a, st);
+  if (a.batch <= 8) return launch_tiny_bt<FP, 8>(a, st);
+  return launch_tiny_bt<FP, kTinyMaxBatch>(a, st);
 }
 
 }  // namespace b200ds
@@ -261,8 +311,7 @@ int b200ds_tiny_train_steps_f32(float* params_dev, float* grads_dev, float* exp_
   a.n_order = n_order; a.first = first;
   a.F = n_features; a.H = hidden; a.batch = batch; a.n_steps = n_steps; a.apply_adam = apply_adam;
   a.lr = lr; a.beta1 = beta1; a.beta2 = beta2;
-  a.b1pow0 = pow(beta1, (double)step0);
-  a.b2pow0 = pow(beta2, (double)step0);
+  a.step0 = step0;
   a.w1 = (float)(1.0 - beta1); a.beta2f = (float)beta2; a.w2 = (float)(1.0 - beta2); a.eps = (float)eps;
   a.losses = losses_dev;
   cudaStream_t st = as_stream(stream);
