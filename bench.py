@@ -120,7 +120,7 @@ class ClockSampler:
 
     def start(self):
         def run():
-            while not self._stop.wait(0.02):
+            while not self._stop.wait(0.01):
                 self.sample()
         self._thr = threading.Thread(target=run, daemon=True)
         self._thr.start()
@@ -316,14 +316,15 @@ def run_ours(a):
         trace("first replay done")
         # untimed: let the SM clock settle under load.  A FIXED replay count: every replay holds a
         # collective, so all ranks must run the same number of them.
+        clk = ClockSampler(local)
+        if rank == 0:             # one sampler per job (NVML queries from 8 processes at once stall the launch threads);
+            clk.start()           # it watches the identical load of the warm-up replays and the timed region
         for _ in range(4000 if wl["H"] <= 4096 else 2000):
             graph.replay()
         barrier()
         trace("clock warm-up replays done")
         K = a.steps
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-        clk = ClockSampler(local)
-        clk.start()
         wall0 = time.perf_counter()
         for i in range(K):
             if not os.environ.get("B200DS_BENCH_NOFLUSH"):
@@ -331,9 +332,8 @@ def run_ours(a):
             evs[i][0].record()
             graph.replay()
             evs[i][1].record()
-            if i % 8 == 7:
-                clk.sample()
-        clk.sample()
+        if rank == 0:
+            clk.sample()          # GPU still busy with the queued steps; nothing NVML-related runs inside the loop
         barrier()
         wall = time.perf_counter() - wall0
         clk.stop()
