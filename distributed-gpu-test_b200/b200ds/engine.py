@@ -46,8 +46,9 @@ def _parse_config(config) -> dict:
     if bool(cfg.get("fp16", {}).get("enabled", False)):
         raise NotImplementedError("fp16 is disabled in the reference (train.py:81); use bf16.enabled for the bf16 extension")
     stage = int(cfg.get("zero_optimization", {}).get("stage", 0))
-    if stage not in (0,):
-        raise NotImplementedError("zero_optimization.stage %d: the reference runs stage 0 (train.py:82)" % stage)
+    if stage not in (0, 1):
+        raise NotImplementedError("zero_optimization.stage %d: the reference runs stage 0 (train.py:82); "
+                                  "stage 1 is the only extension provided" % stage)
     precision = "bf16" if bool(cfg.get("bf16", {}).get("enabled", False)) else "fp32"
     return {"precision": precision, "stage": stage, "train_batch_size": cfg.get("train_batch_size")}
 
@@ -66,7 +67,9 @@ class B200Engine:
         l1, l2 = _find_mlp(model)
         self.F, self.H = l1.in_features, l1.out_features
         self.P = self.F * self.H + 2 * self.H + 1
-        self.Ppad = (self.P + 3) // 4 * 4
+        self.stage = self.cfg["stage"]
+        quantum = 4 * self.le.world_size if self.stage == 1 else 4      # stage 1 shards the flat vector W ways
+        self.Ppad = (self.P + quantum - 1) // quantum * quantum
         if not isinstance(optimizer, torch.optim.Adam) or isinstance(optimizer, torch.optim.AdamW):
             raise NotImplementedError("the reference path uses torch.optim.Adam (train.py:85); got %r" % type(optimizer).__name__)
         if len(optimizer.param_groups) != 1:
@@ -90,8 +93,10 @@ class B200Engine:
         dev = self.device
         self.flat = torch.zeros(self.Ppad, dtype=torch.float32, device=dev)
         self.grads = torch.zeros(self.Ppad, dtype=torch.float32, device=dev)      # the gradient bucket
-        self.exp_avg = torch.zeros(self.Ppad, dtype=torch.float32, device=dev)
-        self.exp_avg_sq = torch.zeros(self.Ppad, dtype=torch.float32, device=dev)
+        # stage 1 (ZeRO-1 style): each rank keeps Adam moments for its 1/W slice of the flat vector only
+        n_state = self.Ppad // self.le.world_size if self.stage == 1 else self.Ppad
+        self.exp_avg = torch.zeros(n_state, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(n_state, dtype=torch.float32, device=dev)
         o = 0
         self._views = []
         for p in (l1.weight, l1.bias, l2.weight, l2.bias):
@@ -104,7 +109,7 @@ class B200Engine:
         assert o == self.P
         stream = _lib.current_stream()
         _lib.check(self.lib.b200ds_broadcast_params(self.ctx, self.flat.data_ptr(), self.P, stream), "broadcast_params")
-        for p, off, n in self._views:     # keep optimizer.state_dict() meaningful
+        for p, off, n in (self._views if self.stage == 0 else []):     # keep optimizer.state_dict() meaningful
             optimizer.state[p] = {"step": torch.tensor(0.0), "exp_avg": self.exp_avg[off:off + n].view(p.shape),
                                   "exp_avg_sq": self.exp_avg_sq[off:off + n].view(p.shape)}
         self._x = None
@@ -198,13 +203,22 @@ class B200Engine:
             _lib.check(self.lib.b200ds_mlp_backward_f32(self.flat.data_ptr(), self._x.data_ptr(), dlogits.data_ptr(), B,
                                                         self.F, self.H, self.grads.data_ptr(), scratch.data_ptr(),
                                                         scratch.numel(), stream), "mlp_backward_f32")
-        # DeepSpeed stage 0: gradients are averaged across ranks before backward() returns
-        _lib.check(self.lib.b200ds_allreduce_bucket(self.ctx, self.grads.data_ptr(), self.P, stream), "allreduce_bucket")
+        if self.stage == 0:
+            # DeepSpeed stage 0: gradients are averaged across ranks before backward() returns
+            _lib.check(self.lib.b200ds_allreduce_bucket(self.ctx, self.grads.data_ptr(), self.P, stream), "allreduce_bucket")
 
     # ------------------------------------------------------------------ train.py:114
     def step(self):
         lr, b1, b2, eps = self._hyper()
         self.global_steps += 1
+        if self.stage == 1:
+            # reduce-scatter -> Adam on this rank's slice -> all-gather of the parameters
+            _lib.check(self.lib.b200ds_zero1_step(self.ctx, self.flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
+                                                  self.exp_avg_sq.data_ptr(), self.Ppad, lr, b1, b2, eps, self.global_steps,
+                                                  _lib.current_stream()), "zero1_step")
+            self._x = None
+            self._logits = None
+            return
         scale = 1.0 / self.le.world_size if self.le.world_size > 1 else 1.0
         _lib.check(self.lib.b200ds_adam_step(self.flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
                                              self.exp_avg_sq.data_ptr(), self.Ppad, lr, b1, b2, eps, self.global_steps,
@@ -225,6 +239,8 @@ class B200Engine:
         Returns the per-step losses (float32 [n_steps], on device)."""
         if not self.supports_fused_steps(batch):
             raise ValueError("fused_steps: shape outside the tiny class (F<=32, H<=256, batch<=32)")
+        if self.stage != 0:
+            raise NotImplementedError("fused_steps runs the reference's stage-0 step")
         if losses is None:
             losses = torch.empty(n_steps, dtype=torch.float32, device=self.device)
         lr, b1, b2, eps = self._hyper()
@@ -259,6 +275,8 @@ class B200Engine:
     def make_host_step(self, batch: int):
         """Pre-allocates what b200ds_train_step_host borrows and returns f(x_host, y_host,
         loss_host) -> None, one end-to-end step over (pinned) host buffers."""
+        if self.stage != 0:
+            raise NotImplementedError("the host-buffer step runs the reference's stage-0 step")
         dev = self.device
         nbytes = self.lib.b200ds_train_step_scratch_bytes(batch, self.F, self.H)
         keep = {
@@ -304,7 +322,7 @@ class B200Engine:
                 sd[names[id(p)]] = flat[off:off + n].view(p.shape).clone()
             state = {
                 "module": sd,
-                "optimizer": {"exp_avg": self.exp_avg[: self.P].cpu(), "exp_avg_sq": self.exp_avg_sq[: self.P].cpu(),
+                "optimizer": {"exp_avg": self.exp_avg.cpu(), "exp_avg_sq": self.exp_avg_sq.cpu(), "zero_stage": self.stage,
                               "step": self.global_steps, "param_groups": [
                                   {k: v for k, v in self.optimizer.param_groups[0].items() if k != "params"}]},
                 "global_steps": self.global_steps,

@@ -30,6 +30,8 @@ const NcclApi* nccl_api() {
   B200_SYM(CommDestroy, "ncclCommDestroy")
   B200_SYM(AllReduce, "ncclAllReduce")
   B200_SYM(Broadcast, "ncclBroadcast")
+  B200_SYM(ReduceScatter, "ncclReduceScatter")
+  B200_SYM(AllGather, "ncclAllGather")
   B200_SYM(GetErrorString, "ncclGetErrorString")
 #undef B200_SYM
   g_api_state = 1;
@@ -165,6 +167,39 @@ int b200ds_allreduce_bucket(b200ds_ctx* ctx, float* bucket_dev, int64_t n, uintp
   if (rc) return rc;
   if (n == 0) return B200DS_OK;
   return b200ds_allreduce_bucket_end(ctx, stream);
+}
+
+// ZeRO-1-style step (BASELINE config 5; the reference itself runs stage 0, train.py:82):
+// reduce-scatter the gradient bucket, Adam on this rank's 1/W slice only (so exp_avg /
+// exp_avg_sq are slice-sized), all-gather the updated parameters.  Same arithmetic per element
+// as stage 0 up to the summation order inside NCCL.
+int b200ds_zero1_step(b200ds_ctx* ctx, float* params_dev, float* grads_dev, float* exp_avg_shard_dev,
+                      float* exp_avg_sq_shard_dev, int64_t n, double lr, double beta1, double beta2, double eps,
+                      int64_t step, uintptr_t stream) {
+  B200_REQUIRE(ctx != nullptr, "zero1_step: null context");
+  B200_REQUIRE(params_dev && grads_dev && exp_avg_shard_dev && exp_avg_sq_shard_dev, "zero1_step: null pointer");
+  const int W = ctx->world;
+  B200_REQUIRE(n > 0 && n % (4 * (int64_t)W) == 0, "zero1_step: n (%lld) must be a positive multiple of 4*world (%d)",
+               (long long)n, 4 * W);
+  const int64_t shard = n / W, off = shard * ctx->rank;
+  if (W == 1)
+    return b200ds_adam_step(params_dev, grads_dev, exp_avg_shard_dev, exp_avg_sq_shard_dev, n, lr, beta1, beta2, eps, step, 1.f, 0, stream);
+  if (!ctx->comm) { set_error("zero1_step: context has no communicator"); return B200DS_ERR_STATE; }
+  const NcclApi* api = nccl_api();
+  if (!api) return B200DS_ERR_NCCL;
+  cudaStream_t s = as_stream(stream);
+  // exchange on the side stream, ordered after the caller's work; the Adam slice runs there too so the
+  // three phases need no round trip through the caller's stream
+  B200_CUDA(cudaEventRecord(ctx->ev_ready, s));
+  B200_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_ready, 0));
+  B200_NCCL(api, api->ReduceScatter(grads_dev, grads_dev + off, (size_t)shard, ncclFloat32, ncclSum, ctx->comm, ctx->side));
+  int rc = b200ds_adam_step(params_dev + off, grads_dev + off, exp_avg_shard_dev, exp_avg_sq_shard_dev, shard, lr, beta1, beta2,
+                            eps, step, (float)(1.0 / W), 0, (uintptr_t)ctx->side);
+  if (rc) return rc;
+  B200_NCCL(api, api->AllGather(params_dev + off, params_dev, (size_t)shard, ncclFloat32, ctx->comm, ctx->side));
+  B200_CUDA(cudaEventRecord(ctx->ev_done, ctx->side));
+  B200_CUDA(cudaStreamWaitEvent(s, ctx->ev_done, 0));
+  return B200DS_OK;
 }
 
 int b200ds_broadcast_params(b200ds_ctx* ctx, float* params_dev, int64_t n, uintptr_t stream) {

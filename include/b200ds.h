@@ -136,6 +136,13 @@ B200DS_API int b200ds_allreduce_bucket(b200ds_ctx* ctx, float* bucket_dev, int64
  * makes `stream` wait for it.  One exchange in flight per context. */
 B200DS_API int b200ds_allreduce_bucket_begin(b200ds_ctx* ctx, float* bucket_dev, int64_t n, uintptr_t stream);
 B200DS_API int b200ds_allreduce_bucket_end(b200ds_ctx* ctx, uintptr_t stream);
+/* ZeRO-1-style optimizer step (BASELINE config 5; an extension -- the reference runs stage 0,
+ * train.py:82): reduce-scatter of the bucket, Adam on this rank's slice [rank*n/W, (rank+1)*n/W)
+ * with slice-sized exp_avg / exp_avg_sq, all-gather of the parameters; replaces
+ * b200ds_allreduce_bucket + b200ds_adam_step.  n % (4*world) == 0.  `step` as in b200ds_adam_step. */
+B200DS_API int b200ds_zero1_step(b200ds_ctx* ctx, float* params_dev, float* grads_dev, float* exp_avg_shard_dev,
+                                 float* exp_avg_sq_shard_dev, int64_t n, double lr, double beta1, double beta2,
+                                 double eps, int64_t step, uintptr_t stream);
 /* Parameter broadcast from rank 0 done by deepspeed.initialize (train.py:87-93). */
 B200DS_API int b200ds_broadcast_params(b200ds_ctx* ctx, float* params_dev, int64_t n, uintptr_t stream);
 /* dist.barrier() at teardown (train.py:134): host-blocking. */

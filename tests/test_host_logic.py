@@ -34,6 +34,7 @@ def test_config_parsing():
                             "zero_optimization": {"stage": 0}})           # train.py:78-83
     assert ok["precision"] == "fp32" and ok["stage"] == 0
     assert eng._parse_config({"bf16": {"enabled": True}})["precision"] == "bf16"
+    assert eng._parse_config({"zero_optimization": {"stage": 1}})["stage"] == 1      # ZeRO-1-style extension (config 5)
     for bad in ({"gradient_accumulation_steps": 2}, {"fp16": {"enabled": True}}, {"zero_optimization": {"stage": 3}}):
         with pytest.raises(NotImplementedError):
             eng._parse_config(bad)
