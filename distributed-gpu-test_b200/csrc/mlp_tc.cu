@@ -88,7 +88,7 @@ gen_batch_kernel(uint4* __restrict__ xq, float* __restrict__ y, int64_t batch, i
       const uint64_t ctr = ctr0 + (uint64_t)(tt >> 2);
       const uint4 r = philox4x32_10(make_uint4((unsigned)ctr, (unsigned)(ctr >> 32), (unsigned)sub, (unsigned)((uint64_t)sub >> 32)), key);
       const float2 p = (tt & 2) ? box_muller(r.z, r.w) : box_muller(r.x, r.y);
-      f = (tt & 1) ? p.y : p.x;
+      f = normal_transform((tt & 1) ? p.y : p.x);
     }
     v[j] = f;
     q[j] = __float2bfloat16(f);

@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(256) philox_normal_kernel(float* __restrict__ 
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       int64_t li = tid + nthreads * (4 * (int64_t)c + k);
-      if (li < numel) out[li] = v[k];
+      if (li < numel) out[li] = normal_transform(v[k]);
     }
   }
 }

@@ -37,6 +37,11 @@ __device__ __forceinline__ float2 box_muller(unsigned a, unsigned b) {
   return r;
 }
 
+// ATen's normal_() finishes with `rand * std + mean` (std = 1, mean = 0) in fp32
+// (ATen/native/cuda/DistributionTemplates.h normal_kernel): a no-op except that it turns the
+// -0.0 Box-Muller produces when u rounds to exactly 1 (sqrt(-2 log 1) = -0.0) into +0.0.
+__device__ __forceinline__ float normal_transform(float r) { return __fadd_rn(__fmul_rn(r, 1.0f), 0.0f); }
+
 // launch geometry ATen would use for `numel` outputs: (grid of 256-thread blocks, Philox calls per thread)
 void philox_plan(int64_t numel, int* grid, int* calls);
 

@@ -82,7 +82,8 @@ def box_muller(a: np.ndarray, b: np.ndarray, branch: np.ndarray) -> np.ndarray:
     v = b.astype(np.float32) * inv2pi + np.float32(inv2pi / np.float32(2))
     s = np.sqrt(np.float32(-2.0) * np.log(u.astype(np.float32))).astype(np.float32)
     r = np.where(branch == 0, np.sin(v), np.cos(v)).astype(np.float32)
-    return (r * s).astype(np.float32)
+    # ATen's normal_() ends with rand * std + mean (std=1, mean=0): turns the -0.0 of u == 1 into +0.0
+    return ((r * s).astype(np.float32) * np.float32(1.0) + np.float32(0.0)).astype(np.float32)
 
 
 def randn(numel: int, seed: int, offset: int, sm_count: int) -> np.ndarray:

@@ -403,3 +403,69 @@ def test_train_py_stdout_matches_reference(golden, tmp_path, extra):
     want = [f"Epoch {e + 1:2d} finished. Avg loss: {v:.4f}" for e, v in enumerate(golden["w1_epoch_means"][0])]
     assert lines == want + ["Training completed."]
     assert os.path.exists(tmp_path / "ck" / "epoch5" / "latest")
+
+
+def test_counted_philox_replays_consecutive_draws(lib, cuda_dev):
+    """b200ds_philox_normal_counted with draw counter k == the (k+1)-th consecutive
+    torch.randn(n) of a generator seeded the same way (what a CUDA-graph replay relies on)."""
+    n, seed = 65536 * 20, 7
+    g = torch.Generator(device=cuda_dev)
+    g.manual_seed(seed)
+    ctr = torch.zeros(1, dtype=torch.int64, device=cuda_dev)
+    out = torch.empty(n, dtype=torch.float32, device=cuda_dev)
+    for k in range(4):
+        want = torch.randn(n, device=cuda_dev, generator=g)
+        ctr.fill_(k)
+        _check(lib, lib.b200ds_philox_normal_counted(out.data_ptr(), n, seed, 0, ctr.data_ptr(), _st()))
+        torch.cuda.synchronize()
+        assert torch.equal(out.view(torch.int32), want.view(torch.int32)), k
+    assert lib.b200ds_philox_normal_counted(out.data_ptr(), n, seed, 0, None, _st()) == 1
+
+
+def test_single_rank_context_exchange_entry_points_are_no_ops(lib, cuda_dev):
+    """world == 1: the all-reduce (whole and in two halves), the broadcast and the barrier return
+    at once and leave the bucket alone; the ZeRO-1-style step degenerates to plain Adam."""
+    ctx = C.c_void_p()
+    _check(lib, lib.b200ds_ctx_create(0, 0, 1, None, C.byref(ctx)))
+    dev, rank, world = C.c_int(-1), C.c_int(-1), C.c_int(-1)
+    _check(lib, lib.b200ds_ctx_info(ctx, C.byref(dev), C.byref(rank), C.byref(world)))
+    assert (dev.value, rank.value, world.value) == (0, 0, 1)
+    n = 1412
+    torch.manual_seed(0)
+    g = torch.randn(n, device=cuda_dev)
+    g0 = g.clone()
+    _check(lib, lib.b200ds_allreduce_bucket(ctx, g.data_ptr(), n, _st()))
+    _check(lib, lib.b200ds_allreduce_bucket_begin(ctx, g.data_ptr(), n, _st()))
+    _check(lib, lib.b200ds_allreduce_bucket_end(ctx, _st()))
+    _check(lib, lib.b200ds_broadcast_params(ctx, g.data_ptr(), n, _st()))
+    _check(lib, lib.b200ds_barrier(ctx))
+    assert torch.equal(g, g0)
+    p1 = torch.randn(n, device=cuda_dev); p2 = p1.clone()
+    m1 = torch.zeros(n, device=cuda_dev); v1 = torch.zeros(n, device=cuda_dev)
+    m2 = torch.zeros(n, device=cuda_dev); v2 = torch.zeros(n, device=cuda_dev)
+    _check(lib, lib.b200ds_zero1_step(ctx, p1.data_ptr(), g.data_ptr(), m1.data_ptr(), v1.data_ptr(), n, 1e-3, 0.9, 0.999, 1e-8, 1, _st()))
+    _check(lib, lib.b200ds_adam_step(p2.data_ptr(), g.data_ptr(), m2.data_ptr(), v2.data_ptr(), n, 1e-3, 0.9, 0.999, 1e-8, 1, 1.0, 0, _st()))
+    torch.cuda.synchronize()
+    assert torch.equal(p1, p2) and torch.equal(m1, m2) and torch.equal(v1, v2)
+    assert lib.b200ds_zero1_step(ctx, p1.data_ptr(), g.data_ptr(), m1.data_ptr(), v1.data_ptr(), 1409, 1e-3, 0.9, 0.999, 1e-8, 1, _st()) == 1
+    assert lib.b200ds_ctx_create(0, 1, 1, None, C.byref(C.c_void_p())) == 1        # rank outside world
+    assert lib.b200ds_ctx_create(0, 0, 2, None, C.byref(C.c_void_p())) == 1        # world 2 without an id
+    _check(lib, lib.b200ds_ctx_destroy(ctx))
+
+
+def test_engine_rejects_what_is_outside_the_path(cuda_dev):
+    import b200ds
+    net = torch.nn.Sequential(torch.nn.Linear(20, 64), torch.nn.ReLU(), torch.nn.Linear(64, 1))
+    with pytest.raises(NotImplementedError):
+        b200ds.initialize(model=net, optimizer=torch.optim.SGD(net.parameters(), lr=0.1), config={})
+    with pytest.raises(NotImplementedError):
+        b200ds.initialize(model=net, optimizer=torch.optim.Adam(net.parameters(), weight_decay=0.1), config={})
+    with pytest.raises(NotImplementedError):
+        b200ds.initialize(model=torch.nn.Linear(20, 1), optimizer=torch.optim.Adam(net.parameters()), config={})
+    engine, _, _, _ = b200ds.initialize(model=net, optimizer=torch.optim.Adam(net.parameters()), config={})
+    with pytest.raises(ValueError):
+        engine(torch.zeros(4, 19, device=cuda_dev))
+    with pytest.raises(ValueError):
+        engine(torch.zeros(4, 20))                       # host tensor: there is no CPU path
+    with pytest.raises(RuntimeError):
+        engine.backward(torch.zeros((), device=cuda_dev))

@@ -185,3 +185,13 @@ def test_label_rule_matches_reference_rule():
     y = ph.labels(x.numpy())
     margin = np.abs(x[:, :10].sum(dim=1).numpy()) > 1e-5
     assert np.array_equal(y[margin], y_ref[margin])
+
+
+def test_philox_negative_zero_edge_case():
+    """Found on the GPU against torch.randn: when the first Philox word is >= 0xFFFFFF80 the uniform
+    rounds to exactly 1, Box-Muller gives sqrt(-2 log 1) = -0.0, and ATen's final `* std + mean`
+    makes it +0.0.  Seed 7, third draw of 65536*20 values (offset 16), elements 50328 / 353432."""
+    w = ph.randn_u32(65536 * 20, 7, 16, 148)
+    assert int(w[50328, 0]) == 0xFFFFFFF2 and int(w[353432, 0]) == 0xFFFFFFF2
+    v = ph.box_muller(w[[50328, 353432], 0], w[[50328, 353432], 1], w[[50328, 353432], 2])
+    assert v.view(np.uint32).tolist() == [0, 0]          # +0.0, not 0x80000000
