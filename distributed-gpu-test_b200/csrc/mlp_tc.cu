@@ -25,6 +25,7 @@
 //                 dW2[n]  = sum_k w1q[n,k] S[n,k]  (= sum_b dz[b] h[b,n]),  db2 = sum_b dz[b].
 #include "common.cuh"
 #include "tc_common.cuh"
+#include <type_traits>
 #include "philox.cuh"
 
 namespace b200ds {
@@ -173,6 +174,9 @@ __device__ __forceinline__ void lane_fold(float (&a)[64], int lane) {
   }
 }
 
+// G = chunks per full/free handshake (one tcgen05.commit and one mbarrier round per G chunks of
+// 128 columns; the accumulator ring is 4 / G groups deep).
+template <int G>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __restrict__ w1q,
                   const float* __restrict__ vlin, const float* __restrict__ w2, const float* __restrict__ b2p,
@@ -185,7 +189,9 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
   float* w2s = reinterpret_cast<float*>(w1s + (size_t)slice_rows * KP * 2);       // [slice_rows] fp32
   unsigned char* xs = reinterpret_cast<unsigned char*>(w2s + slice_rows);         // [stages][8192]
   FwdSmem* sh = reinterpret_cast<FwdSmem*>(xs + kFwdXStages * kTileBytes);
-  const uint32_t n_issuers = NC < 2 ? 1u : 2u;
+  constexpr int RING = kFwdRing / G;                     // accumulator groups in TMEM
+  const int NG = NC / G;                                 // groups per b tile
+  const uint32_t n_issuers = NG < 2 ? 1u : 2u;
 
   if (threadIdx.x == 0) {
     mbar_init(&sh->w_bar, 1);
@@ -218,7 +224,8 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
     sh->v[threadIdx.x] = a;
   }
   __syncthreads();
-  const uint32_t tmem = sh->tmem_slot;
+  if (sh->tmem_slot != 0) __trap();        // all 512 columns are ours: the allocation can only start at 0,
+  constexpr uint32_t tmem = 0;             // and a literal keeps the MMA issue path free of vector -> uniform moves
 
   if (warp == 8) {
     // ===== TMA producer =====
@@ -232,30 +239,37 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
       }
     }
   } else if (warp == 9 || warp == 10) {
-    // ===== MMA issuers (chunk parity): D1T[ring] = w1_chunk . x_tile^T, K = 32.  The whole warp
+    // ===== MMA issuers (group parity): D1T[ring] = w1_chunk . x_tile^T, K = 32.  The whole warp
     // walks the loop (uniform control flow); one elected lane issues.  Two issuing warps because
-    // one warp's wait + issue + commit round is longer than the 132 cycles a chunk executes. =====
-    const int me = warp - 9;
-    if (me < NC) {
+    // one warp's wait + issue + commit round is longer than the MMAs of a group execute.  The body
+    // is instantiated per issuer so that every operand of the issue path is provably warp-uniform
+    // (the issuer shares its scheduler with two FFMA-heavy warps: each instruction it needs costs
+    // several issue slots). =====
+    auto issue = [&](auto me_tag) {
+      constexpr int me = decltype(me_tag)::value;
+      if (me >= NG) return;
       const uint32_t idesc = idesc_bf16(128, 128, 0, 0);
       const uint64_t xdesc0 = smem_desc(smem_u32(xs), LBO_K, SBO_K);
       const uint64_t wdesc0 = smem_desc(smem_u32(w1s), LBO_K, SBO_K);
       mbar_wait(&sh->w_bar, 0);
-      int s = 0; uint32_t xph = 0; int q = 0;
-      for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice) {
+      int s = 0; uint32_t xph = 0; int gq0 = 0;
+      for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice, gq0 += NG) {
         mbar_wait(&sh->x_full[s], xph);
         const uint64_t xd = xdesc0 + (uint64_t)((s * kTileBytes) >> 4);
-        for (int c = 0; c < NC; ++c, ++q) {
-          if ((c & 1) != me) continue;
-          const int r = q % kFwdRing;
-          const uint32_t rph = (uint32_t)(q / kFwdRing) & 1u;
-          const uint64_t wd = wdesc0 + (uint64_t)((c * kTileBytes) >> 4);
-          const uint32_t dcol = tmem + r * 128;
+        for (int g = me; g < NG; g += 2) {
+          const int gq = gq0 + g;
+          const int r = gq % RING;
+          const uint32_t rph = (uint32_t)(gq / RING) & 1u;
+          const uint64_t wd = wdesc0 + (uint64_t)((g * G * kTileBytes) >> 4);
+          const uint32_t dcol = tmem + r * (128 * G);
           mbar_wait(&sh->d1_free[r], rph ^ 1);
           tc_fence_after();
           if (elect_one()) {
-            mma_ss(dcol, wd, xd, idesc, 0);
-            mma_ss(dcol, wd + (2 * LBO_K >> 4), xd + (2 * LBO_K >> 4), idesc, 1);
+#pragma unroll
+            for (int j = 0; j < G; ++j) {
+              mma_ss(dcol + j * 128, wd + (uint64_t)((j * kTileBytes) >> 4), xd, idesc, 0);
+              mma_ss(dcol + j * 128, wd + (uint64_t)((j * kTileBytes + 2 * LBO_K) >> 4), xd + (2 * LBO_K >> 4), idesc, 1);
+            }
             mma_commit(&sh->d1_full[r]);
           }
           __syncwarp();
@@ -264,14 +278,16 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         __syncwarp();
         if (++s == kFwdXStages) { s = 0; xph ^= 1; }
       }
-    }
+    };
+    if (warp == 9) issue(std::integral_constant<int, 0>{});
+    else issue(std::integral_constant<int, 1>{});
   } else {
     // ===== epilogue: 8 warps on every chunk =====
     const int half = warp >> 2, quad = warp & 3;
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     const int row = quad * 32 + lane;                      // the b row this thread finishes (half 0 warps only)
     const float b2 = slice == 0 ? b2p[0] : 0.f;
-    int s = 0; uint32_t xph = 0; int q = 0;
+    int s = 0; uint32_t xph = 0; int gq = 0;
     for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice) {
       float lin = 0.f;
       if (half == 0) {       // linear half of relu: xq[row,:] . v, from the x tile in smem
@@ -297,30 +313,38 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
       // while the FFMAs of the previous piece issue (va: columns 0-31 of the chunk, vb: 32-63).
       uint32_t va[32], vb[32];
       {
-        const int r = q % kFwdRing;
-        mbar_wait(&sh->d1_full[r], (uint32_t)(q / kFwdRing) & 1u);
+        const int r = gq % RING;
+        mbar_wait(&sh->d1_full[r], (uint32_t)(gq / RING) & 1u);
         tc_fence_after();
-        tmem_ld32(tmem + lane_base + r * 128 + half * 64, va);
+        tmem_ld32(tmem + lane_base + r * (128 * G) + half * 64, va);
       }
-      for (int c = 0; c < NC; ++c, ++q) {
-        const int r = q % kFwdRing;
-        const float w2n = w2s[c * kTileRows + quad * 32 + lane];
-        tmem_wait_ld();                                              // va (piece 0 of chunk q) has landed
-        tmem_ld32(tmem + lane_base + r * 128 + half * 64 + 32, vb);  // piece 1 of chunk q
+      for (int g = 0; g < NG; ++g, ++gq) {
+        const int r = gq % RING;
 #pragma unroll
-        for (int i = 0; i < 32; ++i) acc[i] = fmaf(fabsf(__uint_as_float(va[i])), w2n, acc[i]);
-        tmem_wait_ld();                                              // vb has landed: the buffer is fully read
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sh->d1_free[r]);
-        if (c + 1 < NC) {                                            // piece 0 of chunk q+1
-          const int r1 = (q + 1) % kFwdRing;
-          mbar_wait(&sh->d1_full[r1], (uint32_t)((q + 1) / kFwdRing) & 1u);
-          tc_fence_after();
-          tmem_ld32(tmem + lane_base + r1 * 128 + half * 64, va);
+        for (int j = 0; j < G; ++j) {
+          const float w2n = w2s[(g * G + j) * kTileRows + quad * 32 + lane];
+          const uint32_t cbase = tmem + lane_base + r * (128 * G) + j * 128 + half * 64;
+          tmem_wait_ld();                                              // va (piece 0 of this chunk) has landed
+          tmem_ld32(cbase + 32, vb);                                   // piece 1
+#pragma unroll
+          for (int i = 0; i < 32; ++i) acc[i] = fmaf(fabsf(__uint_as_float(va[i])), w2n, acc[i]);
+          tmem_wait_ld();                                              // vb has landed
+          if (j + 1 < G) {
+            tmem_ld32(cbase + 128, va);                                // piece 0 of the next chunk of the group
+          } else {
+            tc_fence_before();                                         // the group is fully read: release it
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sh->d1_free[r]);
+            if (g + 1 < NG) {                                          // piece 0 of the next group
+              const int r1 = (gq + 1) % RING;
+              mbar_wait(&sh->d1_full[r1], (uint32_t)((gq + 1) / RING) & 1u);
+              tc_fence_after();
+              tmem_ld32(tmem + lane_base + r1 * (128 * G) + half * 64, va);
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 32; ++i) acc[32 + i] = fmaf(fabsf(__uint_as_float(vb[i])), w2n, acc[32 + i]);
         }
-#pragma unroll
-        for (int i = 0; i < 32; ++i) acc[32 + i] = fmaf(fabsf(__uint_as_float(vb[i])), w2n, acc[32 + i]);
       }
       // ---- sum over n: 32 lanes by a transposing butterfly, then the 4 quadrants through smem
       lane_fold<64, 16>(acc, lane);
@@ -720,13 +744,15 @@ int b200ds_mlp_forward_tc(const void* xq_dev, const void* wq_dev, const float* p
   int dev = 0;
   B200_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
-    B200_CUDA(cudaFuncSetAttribute(mlp_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    B200_CUDA(cudaFuncSetAttribute(mlp_fwd_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    B200_CUDA(cudaFuncSetAttribute(mlp_fwd_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set[dev & 63] = true;
   }
   if (fp.slices > 1) B200_CUDA(cudaMemsetAsync(logits_dev, 0, sizeof(float) * batch, st));
   const unsigned char* w1q = reinterpret_cast<const unsigned char*>(wq_dev);
   const float* v = reinterpret_cast<const float*>(w1q + (size_t)hidden * KP * 2);
-  mlp_fwd_tc_kernel<<<fp.slices * fp.ctas_per_slice, kFwdThreads, fp.smem, st>>>(
+  auto kern = (fp.slice_rows / kTileRows) % 2 == 0 ? mlp_fwd_tc_kernel<2> : mlp_fwd_tc_kernel<1>;
+  kern<<<fp.slices * fp.ctas_per_slice, kFwdThreads, fp.smem, st>>>(
       reinterpret_cast<const unsigned char*>(xq_dev), w1q, v, params_dev + L.off_w2(), params_dev + L.off_b2(), logits_dev,
       fp.n_btiles, fp.slice_rows, fp.slices, fp.ctas_per_slice);
   B200_LAUNCH_CHECK();

@@ -3,9 +3,10 @@
 // loop until the MMAs are done, one of: nothing | FFMA only | tcgen05.ld only | both.
 #include "../distributed-gpu-test_b200/csrc/tc_common.cuh"
 #include <cstdio>
+#include <cstdlib>
 using namespace b200ds::tc;
 
-__global__ void __launch_bounds__(320, 1) k(long long* out, int mode, float* sink) {
+__global__ void __launch_bounds__(320, 1) k(long long* out, int mode, float* sink, int wmask) {
   extern __shared__ __align__(1024) unsigned char smem[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t slot;
@@ -37,7 +38,7 @@ __global__ void __launch_bounds__(320, 1) k(long long* out, int mode, float* sin
     mbar_wait(&bar, 0);
     tc_fence_after();
     if (lane == 0) { out[0] = clock64() - t0; done = 1; }
-  } else if (warp < 8) {
+  } else if (warp < 8 && ((wmask >> warp) & 1)) {
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     float acc[64];
 #pragma unroll
@@ -78,7 +79,7 @@ int main() {
   const char* names[4] = {"epilogue warps idle-spin", "FFMA only", "tcgen05.ld only", "tcgen05.ld + FFMA"};
   for (int rep = 0; rep < 2; ++rep)
     for (int m = 0; m < 4; ++m) {
-      k<<<1, 320, 17 * 8192 + 1024>>>(d, m, sink);
+      k<<<(getenv("GRID") ? atoi(getenv("GRID")) : 1), 320, 17 * 8192 + 1024>>>(d, m, sink, getenv("WMASK") ? (int)strtol(getenv("WMASK"), 0, 16) : 0xff);
       if (cudaDeviceSynchronize() != cudaSuccess) { printf("error\n"); return 1; }
       long long h[2]; cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost);
       if (rep) printf("%-26s: 112 chunks in %lld cycles = %.1f / chunk; epilogue loop iterations %lld (%.1f cycles each)\n", names[m], h[0], h[0] / 112.0, h[1], h[1] ? (double)h[0] / h[1] : 0.0);
