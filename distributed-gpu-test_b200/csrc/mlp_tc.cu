@@ -309,8 +309,8 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
       float acc[64];
 #pragma unroll
       for (int i = 0; i < 64; ++i) acc[i] = 0.f;
-      // Software pipeline across chunks: the TMEM load of one 32-column piece is always in flight
-      // while the FFMAs of the previous piece issue (va: columns 0-31 of the chunk, vb: 32-63).
+      // Software pipeline across chunks: the TMEM load of one 32-column piece is in flight while
+      // the FFMAs of the previous piece issue (va: columns 0-31 of the chunk, vb: 32-63).
       uint32_t va[32], vb[32];
       {
         const int r = gq % RING;
@@ -373,7 +373,7 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
 }
 
 // ------------------------------------------------------------------ backward
-constexpr int kBwdXStages = 4;
+constexpr int kBwdXStages = 12;
 constexpr int kBwdRing = 3;               // D1T accumulators: 3 x 128 columns (cols 0..383)
 constexpr int kBwdNB = 4;                 // n blocks per CTA: S accumulators 4 x 32 columns (cols 384..511)
 constexpr int kBwdThreads = 32 * 12;      // 0-7 epilogue (two groups), 8 TMA + dz stager, 9 MMA1, 10-11 MMA2 (n block parity);
@@ -424,13 +424,19 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
     }
     int s = 0; uint32_t ph = 0;
     float dsum = 0.f;
+    // dz is read three tiles ahead: a global load in this serial loop would otherwise put its
+    // whole latency into every tile
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto dz_tile = [&](int t) { return t < t_end ? __ldg(reinterpret_cast<const float4*>(dz + (size_t)t * kTileRows) + lane) : zero4; };
+    float4 d0 = dz_tile(t_begin), d1 = dz_tile(t_begin + 1), d2 = dz_tile(t_begin + 2);
     for (int t = t_begin; t < t_end; ++t) {
       mbar_wait(&sh->x_free[s], ph ^ 1);
       if (lane == 0) {
         mbar_arrive_expect_tx(&sh->x_full[s], kTileBytes);
         tma_load_1d(xs + s * kTileBytes, xq + (size_t)t * kTileBytes, kTileBytes, &sh->x_full[s]);
       }
-      float4 d = *reinterpret_cast<const float4*>(dz + (size_t)t * kTileRows + lane * 4);
+      const float4 d = d0;
+      d0 = d1; d1 = d2; d2 = dz_tile(t + 3);
       dsum += (d.x + d.y) + (d.z + d.w);
       __nv_bfloat162 p0 = __floats2bfloat162_rn(d.x, d.y), p1 = __floats2bfloat162_rn(d.z, d.w);
       sh->dzs[s][lane * 2 + 0] = *reinterpret_cast<uint32_t*>(&p0);

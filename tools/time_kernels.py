@@ -34,4 +34,4 @@ for name, fn in (("fwd", fwd), ("bwd+finish", bwd)):
     e0.record()
     for _ in range(n): fn()
     e1.record(); torch.cuda.synchronize()
-    print(f"{os.environ.get('B200DS_LIB','default'):28s} B={B} H={H} {name:11s} {1e3 * e0.elapsed_time(e1) / n:8.2f} us", flush=True)
+    print(f"{os.environ.get('B200DS_LIB','default'):28s} B={B} H={H} {name:14s} {1e3 * e0.elapsed_time(e1) / n:8.2f} us", flush=True)
