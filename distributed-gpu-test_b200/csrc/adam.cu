@@ -36,6 +36,18 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
             int64_t n, AdamScalars s, double lr, double beta1, double beta2, int64_t step,
             const unsigned long long* __restrict__ step_counter, int zero_grad) {
   __shared__ float sh[2];
+  const int64_t nvec = n >> 2;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float4* p4 = reinterpret_cast<float4*>(p);
+  float4* g4 = reinterpret_cast<float4*>(g);
+  float4* m4 = reinterpret_cast<float4*>(m);
+  float4* v4 = reinterpret_cast<float4*>(v);
+  // the first vectors are requested before the block waits for thread 0's two double-precision
+  // pow(): their latency and the loads' overlap instead of adding up
+  int64_t i = t0;
+  float4 pv, gv, mv, vv;
+  if (i < nvec) { pv = p4[i]; gv = g4[i]; mv = m4[i]; vv = v4[i]; }
   if (threadIdx.x == 0) {
     double t = kCounted ? (double)(*step_counter) : (double)step;
     double bc1 = 1.0 - pow(beta1, t);
@@ -45,21 +57,15 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
   }
   __syncthreads();
   const float neg_step_size = sh[0], bc2_sqrt = sh[1];
-  const int64_t nvec = n >> 2;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  float4* p4 = reinterpret_cast<float4*>(p);
-  float4* g4 = reinterpret_cast<float4*>(g);
-  float4* m4 = reinterpret_cast<float4*>(m);
-  float4* v4 = reinterpret_cast<float4*>(v);
-  for (int64_t i = t0; i < nvec; i += stride) {
-    float4 pv = p4[i], gv = g4[i], mv = m4[i], vv = v4[i];
+  while (i < nvec) {
     adam_one(pv.x, gv.x, mv.x, vv.x, s, neg_step_size, bc2_sqrt);
     adam_one(pv.y, gv.y, mv.y, vv.y, s, neg_step_size, bc2_sqrt);
     adam_one(pv.z, gv.z, mv.z, vv.z, s, neg_step_size, bc2_sqrt);
     adam_one(pv.w, gv.w, mv.w, vv.w, s, neg_step_size, bc2_sqrt);
     p4[i] = pv; m4[i] = mv; v4[i] = vv;
     if (zero_grad) g4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    i += stride;
+    if (i < nvec) { pv = p4[i]; gv = g4[i]; mv = m4[i]; vv = v4[i]; }
   }
   for (int64_t i = (nvec << 2) + t0; i < n; i += stride) {
     float pv = p[i], mv = m[i], vv = v[i];
