@@ -65,48 +65,59 @@ pack_x_kernel(const float* __restrict__ x, int64_t batch, int F, uint4* __restri
 // the device every step).  Element (row, k) is element li = row*F + k of
 // torch.randn(B*F, device='cuda') under (seed, offset): Philox counter offset/4 + li/(4*nthreads),
 // subsequence li % nthreads, output (li / nthreads) % 4 -- the mapping of philox_normal_kernel.
-// One thread = one 16-byte chunk of xq (same thread->address map as pack_x_kernel); the label
-// rule (train.py:22-23) is evaluated on the fp32 values in the order label_rule_kernel uses,
-// the values of the second chunk arriving by shuffle.  fp32 x is never written.
+// Four threads per row.  Each draws ceil(F/4) of the row's values (an even split: one Philox
+// evaluation + Box-Muller per value is the whole cost of the kernel), the row is assembled in
+// shared memory, and each thread then writes one 16-byte chunk of xq (same thread->address
+// map as pack_x_kernel); thread 0 of the row evaluates the label rule (train.py:22-23) on the
+// fp32 values in the order label_rule_kernel uses.  fp32 x is never written to global memory.
 template <typename idx_t>      // uint32_t when batch*F < 2^31 (64-bit div/mod would dominate the kernel)
 __global__ void __launch_bounds__(256)
 gen_batch_kernel(uint4* __restrict__ xq, float* __restrict__ y, int64_t batch, int F, uint2 key, uint64_t ctr0,
-                 int64_t nthreads, int calls, const unsigned long long* __restrict__ draw_counter) {
+                 int64_t nthreads, uint32_t inv_nthreads /* floor(2^32 / nthreads) */, int calls,
+                 const unsigned long long* __restrict__ draw_counter) {
+  __shared__ float xs[64][33];                                           // the block's 64 rows, fp32
   if (draw_counter) ctr0 += (uint64_t)(*draw_counter) * (uint64_t)calls;
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;      // batch % 8 == 0: whole warps only
   const int r8 = (int)(t & 7), c = (int)((t >> 3) & 3);
   const int64_t row = ((t >> 5) << 3) + r8;
-  float v[8];
+  if (row >= batch) return;                                              // whole warps (batch % 8 == 0)
+  float* xr = xs[(threadIdx.x >> 5) * 8 + r8];
+  const int per = (F + 3) >> 2;                                          // values drawn by each of the 4 threads
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int k = c * per + j;
+    if (j < per && k < F) {
+      const idx_t li = (idx_t)row * (idx_t)F + (idx_t)k;
+      idx_t tt, sub;
+      if (sizeof(idx_t) == 4) {                                          // li / nthreads by multiply-high and one correction
+        uint32_t qd = __umulhi((uint32_t)li, inv_nthreads);
+        uint32_t rm = (uint32_t)li - qd * (uint32_t)nthreads;
+        if (rm >= (uint32_t)nthreads) { ++qd; rm -= (uint32_t)nthreads; }
+        tt = (idx_t)qd; sub = (idx_t)rm;
+      } else {
+        tt = li / (idx_t)nthreads;
+        sub = li - tt * (idx_t)nthreads;
+      }
+      const uint64_t ctr = ctr0 + (uint64_t)(tt >> 2);
+      const uint4 r = philox4x32_10(make_uint4((unsigned)ctr, (unsigned)(ctr >> 32), (unsigned)sub, (unsigned)((uint64_t)sub >> 32)), key);
+      const float2 p = (tt & 2) ? box_muller(r.z, r.w) : box_muller(r.x, r.y);
+      xr[k] = normal_transform((tt & 1) ? p.y : p.x);
+    }
+  }
+  __syncwarp();                                                          // the 4 threads of a row share a warp
   __nv_bfloat16 q[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int k = c * 8 + j;
-    float f = k < F + 2 ? 1.f : 0.f;
-    if (k < F) {
-      const idx_t li = (idx_t)row * (idx_t)F + (idx_t)k;
-      const idx_t tt = li / (idx_t)nthreads;
-      const idx_t sub = li - tt * (idx_t)nthreads;
-      const uint64_t ctr = ctr0 + (uint64_t)(tt >> 2);
-      const uint4 r = philox4x32_10(make_uint4((unsigned)ctr, (unsigned)(ctr >> 32), (unsigned)sub, (unsigned)((uint64_t)sub >> 32)), key);
-      const float2 p = (tt & 2) ? box_muller(r.z, r.w) : box_muller(r.x, r.y);
-      f = normal_transform((tt & 1) ? p.y : p.x);
-    }
-    v[j] = f;
-    q[j] = __float2bfloat16(f);
+    q[j] = __float2bfloat16(k < F ? xr[k] : (k < F + 2 ? 1.f : 0.f));
   }
   xq[t] = *reinterpret_cast<uint4*>(q);
-  // label: sum of columns 0 .. F/2-1 in index order (F/2 <= 15: chunk 0 and part of chunk 1)
-  float acc = 0.f;
-  const int half = F >> 1;
-#pragma unroll
-  for (int j = 0; j < 8; ++j)
-    if (j < half) acc += v[j];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const float nxt = __shfl_down_sync(0xffffffffu, v[j], 8);     // column 8 + j of the same row
-    if (8 + j < half) acc += nxt;
+  if (c == 0) {      // label: sum of columns 0 .. F/2-1 in index order
+    float acc = 0.f;
+    const int half = F >> 1;
+    for (int k = 0; k < half; ++k) acc += xr[k];
+    y[row] = acc > 0.f ? 1.f : 0.f;
   }
-  if (c == 0) y[row] = acc > 0.f ? 1.f : 0.f;
 }
 
 constexpr int kPackRows = 64;             // rows of W1 per pack_w1 block (256 threads = 64 rows x 4 k chunks)
@@ -700,11 +711,12 @@ static int launch_gen_batch(void* xq_dev, float* y_dev, int64_t batch, int n_fea
   const uint2 key = make_uint2((unsigned)seed, (unsigned)(seed >> 32));
   if (batch * n_features < (int64_t)1 << 31)
     gen_batch_kernel<uint32_t><<<blocks, 256, 0, as_stream(stream)>>>(
-        reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256, calls,
+        reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256,
+        (uint32_t)(((uint64_t)1 << 32) / ((uint64_t)grid * 256)), calls,
         reinterpret_cast<const unsigned long long*>(draw_counter_dev));
   else
     gen_batch_kernel<uint64_t><<<blocks, 256, 0, as_stream(stream)>>>(
-        reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256, calls,
+        reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256, 0u, calls,
         reinterpret_cast<const unsigned long long*>(draw_counter_dev));
   B200_LAUNCH_CHECK();
   if (offset_advance) *offset_advance = (uint64_t)calls * 4;

@@ -22,12 +22,14 @@ _lib.check(lib.b200ds_pack_x_bf16(x.data_ptr(), B, F, xq.data_ptr(), st))
 _lib.check(lib.b200ds_pack_params_bf16(params.data_ptr(), F, H, wq.data_ptr(), st))
 def fwd(): _lib.check(lib.b200ds_mlp_forward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), B, F, H, z.data_ptr(), st))
 def bwd(): _lib.check(lib.b200ds_mlp_backward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), dz.data_ptr(), B, F, H, g.data_ptr(), sc.data_ptr(), sc.numel(), st))
+yb = torch.empty(B, device=dev)
+def gen(): _lib.check(lib.b200ds_gen_batch_bf16(xq.data_ptr(), yb.data_ptr(), B, F, 1234, 0, None, st))
 # spin the clocks up
 t0 = time.time()
 while time.time() - t0 < 1.0:
     fwd(); bwd()
 torch.cuda.synchronize()
-for name, fn in (("fwd", fwd), ("bwd+finish", bwd)):
+for name, fn in (("gen_batch", gen), ("fwd", fwd), ("bwd+finish", bwd)):
     for _ in range(5): fn()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n = 50
