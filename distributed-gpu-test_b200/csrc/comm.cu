@@ -121,6 +121,8 @@ int b200ds_ctx_destroy(b200ds_ctx* c) {
   if (!c) return B200DS_OK;
   cudaSetDevice(c->device);
   if (c->side) cudaStreamSynchronize(c->side);
+  if (c->copy) { cudaStreamSynchronize(c->copy); cudaStreamDestroy(c->copy); }
+  if (c->ev_copied) cudaEventDestroy(c->ev_copied);
   if (c->comm) { const NcclApi* api = nccl_api(); if (api) api->CommDestroy(c->comm); }
   if (c->ev_ready) cudaEventDestroy(c->ev_ready);
   if (c->ev_done) cudaEventDestroy(c->ev_done);

@@ -13,6 +13,13 @@ struct b200ds_ctx {
   cudaEvent_t ev_done = nullptr;     // all-reduce complete on the side stream
   int64_t* iota = nullptr;           // device [32] = 0..31, identity order for the host-buffer step
   float* barrier_word = nullptr;     // device scratch for b200ds_barrier
+  // host-batch prefetch (b200ds_train_step_host_prefetch): copy stream, "copy landed" event,
+  // which host batch sits in which half of the staging buffers
+  cudaStream_t copy = nullptr;
+  cudaEvent_t ev_copied = nullptr;
+  const float* pf_x = nullptr;
+  const float* pf_y = nullptr;
+  int pf_slot = 0;
 };
 
 namespace b200ds {

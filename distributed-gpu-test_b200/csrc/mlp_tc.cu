@@ -537,15 +537,16 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         tc_fence_after();
         const uint4* dzp = reinterpret_cast<const uint4*>(sh->dzs[s]);
         const uint32_t tbase = tmem + lane_base + r * 128;
-        uint32_t va[32], vb[32];
+        uint32_t va[32], vb[32], vc[32];
         uint4 d4[4];
+        // A tcgen05.wait::ld round costs ~200 cycles and waits for every outstanding load: the four
+        // 32-column pieces go through three register buffers so that only two rounds are exposed,
+        // the second with its loads already 64 / 128 instructions old.
         tmem_ld32(tbase, va);
-        // piece j: dz pairs loaded and the next TMEM load issued before this piece is converted
-#define B200_BWD_PIECE(J, CUR, NXT)                                                               \
+        tmem_ld32(tbase + 32, vb);
+#define B200_BWD_CONVERT(J, CUR)                                                                   \
         {                                                                                          \
           _Pragma("unroll") for (int c4 = 0; c4 < 4; ++c4) d4[c4] = dzp[(J) * 4 + c4];            \
-          tmem_wait_ld();                                                                          \
-          if ((J) < 3) tmem_ld32(tbase + ((J) + 1) * 32, NXT);                                     \
           uint32_t p[16];                                                                          \
           _Pragma("unroll") for (int c4 = 0; c4 < 4; ++c4) {                                      \
             const uint32_t dd[4] = {d4[c4].x, d4[c4].y, d4[c4].z, d4[c4].w};                       \
@@ -558,11 +559,15 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
           }                                                                                        \
           tmem_st16(tbase + (J) * 16, p);                                                          \
         }
-        B200_BWD_PIECE(0, va, vb)
-        B200_BWD_PIECE(1, vb, va)
-        B200_BWD_PIECE(2, va, vb)
-        B200_BWD_PIECE(3, vb, va)
-#undef B200_BWD_PIECE
+        tmem_wait_ld();                          // pieces 0 and 1
+        tmem_ld32(tbase + 64, vc);
+        B200_BWD_CONVERT(0, va)
+        tmem_ld32(tbase + 96, va);
+        B200_BWD_CONVERT(1, vb)
+        tmem_wait_ld();                          // pieces 2 and 3
+        B200_BWD_CONVERT(2, vc)
+        B200_BWD_CONVERT(3, va)
+#undef B200_BWD_CONVERT
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();

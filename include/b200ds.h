@@ -253,6 +253,20 @@ B200DS_API int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* b
                            const float* x_host, const float* y_host, int64_t batch,
                            int n_features, int hidden, double lr, double beta1, double beta2,
                            double eps, int64_t step0, float* loss_host, uintptr_t stream);
+/* The same step with the NEXT batch's host->device copy started on the context's own copy
+ * stream before this batch is computed -- what DataLoader workers + pin_memory give the
+ * reference loop (train.py:36-44,104): the copy of batch k+1 hides behind the kernels of batch
+ * k.  x_stage / y_stage must hold TWO batches (2*batch*F and 2*batch floats).  The call whose
+ * (x_host, y_host) are the pointers given as (x_next_host, y_next_host) by the previous call
+ * uses the staged copy and copies nothing; any other pointers are copied as in
+ * b200ds_train_step_host.  A prefetched host buffer must stay unchanged until the call that
+ * consumes it returns.  NULL next pointers = no prefetch.  Result per call: identical to
+ * b200ds_train_step_host on the same batch. */
+B200DS_API int b200ds_train_step_host_prefetch(b200ds_ctx* ctx, const b200ds_step_bufs* bufs,
+                           const float* x_host, const float* y_host,
+                           const float* x_next_host, const float* y_next_host, int64_t batch,
+                           int n_features, int hidden, double lr, double beta1, double beta2,
+                           double eps, int64_t step0, float* loss_host, uintptr_t stream);
 
 #ifdef __cplusplus
 }

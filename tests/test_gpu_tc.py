@@ -181,6 +181,58 @@ def test_host_buffer_step_tc_path(lib, cuda_dev):
     _chk(lib.b200ds_ctx_destroy(ctx))
 
 
+def _host_step_state(lib, dev, B, F, H, stage_batches):
+    from b200ds import _lib
+    torch.manual_seed(11)
+    flat = ora.flatten(ora.init_params(F, H))
+    P = flat.numel(); Ppad = (P + 3) // 4 * 4
+    z = lambda n: torch.zeros(n, dtype=torch.float32, device=dev)      # noqa: E731
+    t = dict(params=z(Ppad), grads=z(Ppad), m=z(Ppad), v=z(Ppad), xs=z(stage_batches * B * F), ys=z(stage_batches * B),
+             lg=z(B), dl=z(B), ls=z(1),
+             sc=torch.zeros(max(256, lib.b200ds_train_step_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev),
+             xq=torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=dev),
+             wq=torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=dev))
+    t["params"][:P] = flat.to(dev)
+    bufs = _lib.StepBufs(t["params"].data_ptr(), t["grads"].data_ptr(), t["m"].data_ptr(), t["v"].data_ptr(),
+                         t["xs"].data_ptr(), t["ys"].data_ptr(), t["lg"].data_ptr(), t["dl"].data_ptr(), t["ls"].data_ptr(),
+                         t["sc"].data_ptr(), t["sc"].numel(), t["xq"].data_ptr(), t["wq"].data_ptr())
+    return t, bufs, P
+
+
+@pytest.mark.parametrize("B,F,H", [(512, 20, 256), (4, 20, 64)])
+def test_prefetching_host_step_equals_the_plain_one(lib, cuda_dev, B, F, H):
+    """b200ds_train_step_host_prefetch: same losses and parameters, bit for bit, as
+    b200ds_train_step_host over the same batches -- with the next batch announced, with a
+    batch that was NOT the announced one (prefetch discarded), and with no announcement."""
+    torch.manual_seed(3)
+    n = 6
+    xh = [torch.randn(B, F).pin_memory() for _ in range(n)]
+    yh = [ora.label_rule(x).reshape(-1).contiguous().pin_memory() for x in xh]
+    lh = torch.zeros(1).pin_memory()
+    order = [0, 1, 2, 4, 5, 3]               # step 3 consumes batch 4 although batch 3 was announced
+    announce = [1, 2, 3, 5, None, None]      # step 4 announces nothing, step 5 arrives unannounced
+    res = []
+    for prefetch in (False, True):
+        t, bufs, P = _host_step_state(lib, cuda_dev, B, F, H, 2 if prefetch else 1)
+        ctx = C.c_void_p()
+        _chk(lib.b200ds_ctx_create(0, 0, 1, None, C.byref(ctx)))
+        losses = []
+        for step, (i, nxt) in enumerate(zip(order, announce)):
+            if prefetch:
+                xn = xh[nxt].data_ptr() if nxt is not None else None
+                yn = yh[nxt].data_ptr() if nxt is not None else None
+                _chk(lib.b200ds_train_step_host_prefetch(ctx, C.byref(bufs), xh[i].data_ptr(), yh[i].data_ptr(), xn, yn, B, F, H,
+                                                         1e-3, 0.9, 0.999, 1e-8, step, lh.data_ptr(), _st()))
+            else:
+                _chk(lib.b200ds_train_step_host(ctx, C.byref(bufs), xh[i].data_ptr(), yh[i].data_ptr(), B, F, H,
+                                                1e-3, 0.9, 0.999, 1e-8, step, lh.data_ptr(), _st()))
+            losses.append(float(lh))
+        res.append((losses, t["params"][:P].cpu().clone()))
+        _chk(lib.b200ds_ctx_destroy(ctx))
+    assert res[0][0] == res[1][0]
+    assert torch.equal(res[0][1], res[1][1])
+
+
 @pytest.mark.parametrize("B,F", [(128, 20), (65536, 20), (1024, 30), (256, 1), (4096, 7)])
 def test_fused_batch_generator_is_bit_identical_to_the_three_kernel_path(lib, cuda_dev, B, F):
     """b200ds_gen_batch_bf16 == philox_normal -> label_rule -> pack_x, byte for byte, also at a
