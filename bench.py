@@ -207,6 +207,12 @@ class WideStep:
             self.dominant = dict(name="mlp_bwd_tc_kernel", bound="tensor")
         # bf16: gen_batch, pack_w1, forward, loss, backward, finish, adam; fp32: philox, label, forward, loss, backward, finish, adam
         self.launches_per_step = 7
+        # W > 1: gradient exchange + Adam as one peer-memory kernel (NVLink loads of the peers' buckets,
+        # fixed summation order); B200DS_BENCH_NCCL=1 selects ncclAllReduce + the Adam kernel instead
+        self.p2p = world > 1 and not os.environ.get("B200DS_BENCH_NCCL")
+        if self.p2p:
+            _lib.check(lib.b200ds_ctx_enable_p2p(ctx, self.Ppad))
+            self.side = torch.cuda.Stream(device=dev)
 
     def step(self, st, ev_pair=None):
         lib, chk = self.lib, self._lib.check
@@ -238,6 +244,20 @@ class WideStep:
                                             self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
         if ev_pair:
             ev_pair[1].record()
+        if self.p2p:
+            # the exchange kernel (mostly waiting on NVLink round trips, at most one CTA per SM) runs on a
+            # side stream while the next batch is generated here; both are done before the next step starts
+            main = torch.cuda.current_stream()
+            fork = torch.cuda.Event(); fork.record(main)
+            self.side.wait_event(fork)
+            chk(lib.b200ds_allreduce_adam_p2p(self.ctx, self.params.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),
+                                              self.v.data_ptr(), self.Ppad, LR, 0.9, 0.999, 1e-8, 0, self.counter.data_ptr(),
+                                              self.side.cuda_stream))
+            join = torch.cuda.Event(); join.record(self.side)
+            if self.tc:
+                self.gen_next(st)
+            main.wait_event(join)
+            return
         if self.tc:
             # the next batch does not need this step's gradients: it is generated on the main stream
             # while the all-reduce runs on the context's side stream (the backward is done with xq)
@@ -375,7 +395,9 @@ def run_ours(a):
                                             f"generated on device (Philox4x32-10), Adam, {world} rank(s)",
                                 "per_gpu_batch": wl["B"], "n_features": wl["F"], "hidden": wl["H"], "parallelism": f"dp{world}",
                                 "l2": "256 MiB device buffer rewritten between timed steps, outside the per-step CUDA-event brackets",
-                                "timing": "each step = one CUDA-graph replay of the whole step (all kernels + NCCL all-reduce), "
+                                "exchange": ("peer-memory all-reduce + Adam in one kernel (b200ds_allreduce_adam_p2p)" if ws.p2p else
+                                             "ncclAllReduce on a side stream + Adam kernel") if world > 1 else "none (1 rank)",
+                                "timing": "each step = one CUDA-graph replay of the whole step (all kernels + the gradient exchange), "
                                           "bracketed by CUDA events on the launching stream; sum over steps, max over ranks"},
                         dtype="f32" if precision == "fp32" else "bf16"))
         if not a.no_tiny and rank == 0 and world == 1:

@@ -8,27 +8,9 @@
 //   denom = sqrt(v)/sqrt(1-b2^t) + eps;  p.addcdiv_(m, denom, -lr/(1-b1^t))
 // with the bias corrections formed in double and rounded to fp32 once, as torch does when
 // it passes Python floats to fp32 kernels.
-#include "common.cuh"
+#include "adam.cuh"
 
 namespace b200ds {
-
-struct AdamScalars {
-  float w1;         // 1 - beta1        (lerp weight)
-  float beta2;
-  float w2;         // 1 - beta2
-  float eps;
-  float grad_scale; // 1/world (stage-0 averaging folded in), 1 otherwise
-};
-
-__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamScalars& s,
-                                         float neg_step_size, float bc2_sqrt) {
-  g *= s.grad_scale;
-  m = fmaf(s.w1, g - m, m);                 // lerp, weight < 0.5 branch
-  v = v * s.beta2;
-  v = fmaf(s.w2 * g, g, v);                 // addcmul: v + (value*g)*g
-  float denom = sqrtf(v) / bc2_sqrt + s.eps;
-  p = fmaf(neg_step_size, m / denom, p);    // addcdiv: p + value*(m/denom)
-}
 
 template <bool kCounted>
 __global__ void __launch_bounds__(256)

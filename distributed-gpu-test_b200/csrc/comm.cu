@@ -122,6 +122,16 @@ int b200ds_ctx_destroy(b200ds_ctx* c) {
   cudaSetDevice(c->device);
   if (c->side) cudaStreamSynchronize(c->side);
   if (c->copy) { cudaStreamSynchronize(c->copy); cudaStreamDestroy(c->copy); }
+  if (c->p2p_own) {
+    cudaDeviceSynchronize();
+    for (int w = 0; w < c->world && w < B200DS_P2P_MAX_WORLD; ++w) {
+      if (w == c->rank) continue;
+      if (c->p2p_xchg[w]) cudaIpcCloseMemHandle(c->p2p_xchg[w]);
+      if (c->p2p_flags[w]) cudaIpcCloseMemHandle(c->p2p_flags[w]);
+    }
+    if (c->p2p_xchg[c->rank]) cudaFree(c->p2p_xchg[c->rank]);
+    if (c->p2p_flags[c->rank]) cudaFree(c->p2p_flags[c->rank]);
+  }
   if (c->ev_copied) cudaEventDestroy(c->ev_copied);
   if (c->comm) { const NcclApi* api = nccl_api(); if (api) api->CommDestroy(c->comm); }
   if (c->ev_ready) cudaEventDestroy(c->ev_ready);

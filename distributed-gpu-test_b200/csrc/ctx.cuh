@@ -20,6 +20,12 @@ struct b200ds_ctx {
   const float* pf_x = nullptr;
   const float* pf_y = nullptr;
   int pf_slot = 0;
+  // peer-memory exchange (b200ds_ctx_enable_p2p): every rank's exchange buffer and flag row,
+  // own entries cudaMalloc'ed here, the others opened from the peers' IPC handles
+  float* p2p_xchg[B200DS_P2P_MAX_WORLD] = {};
+  unsigned long long* p2p_flags[B200DS_P2P_MAX_WORLD] = {};
+  int64_t p2p_cap = 0;               // floats per half of an exchange buffer; 0 = not enabled
+  bool p2p_own = false;
 };
 
 namespace b200ds {

@@ -60,6 +60,9 @@ static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const flo
     if ((rc = b200ds_mlp_backward_f32(b->params, x_dev, b->dlogits, batch, n_features, hidden, b->grads,
                                       sc + bce_bytes, b->scratch_bytes - bce_bytes, stream))) return rc;
   }
+  if (ctx->world > 1 && ctx->p2p_cap >= Ppad)      // peer-memory exchange enabled on this context: one kernel for both
+    return b200ds_allreduce_adam_p2p(ctx, b->params, b->grads, b->exp_avg, b->exp_avg_sq, Ppad, lr, beta1, beta2, eps,
+                                     step0 + 1, nullptr, stream);
   if ((rc = b200ds_allreduce_bucket(ctx, b->grads, P, stream))) return rc;
   return b200ds_adam_step(b->params, b->grads, b->exp_avg, b->exp_avg_sq, Ppad, lr, beta1, beta2, eps,
                           step0 + 1, scale, 0, stream);

@@ -230,6 +230,25 @@ B200DS_API int b200ds_mlp_backward_tc(const void* xq_dev, const void* wq_dev, co
                                       float* grads_dev, void* scratch_dev, size_t scratch_bytes,
                                       uintptr_t stream);
 
+/* ---- gradient exchange + optimizer step over NVLink peer memory ---------------------
+ * model_engine.backward's all-reduce and model_engine.step()'s Adam (train.py:113-114) as ONE
+ * kernel: every rank publishes its gradient bucket in a buffer its peers have mapped (CUDA
+ * IPC), waits on arrival flags, reads all W buckets through NVLink, sums them in rank order,
+ * applies 1/W and Adam.  No collective-library call on the step; parameters stay bit-equal
+ * across ranks (fixed summation order).  grads_dev ends up holding the SUM, as after
+ * b200ds_allreduce_bucket.  b200ds_ctx_enable_p2p is collective (every rank of the context
+ * calls it once, with the same max_elems), allocates the exchange buffer (8 * max_elems bytes)
+ * and exchanges the handles through the context's communicator; at most B200DS_P2P_MAX_WORLD
+ * ranks, all on one NVLink domain.  n: multiple of 4, <= max_elems.  step / step_counter_dev
+ * as in b200ds_adam_step / b200ds_adam_step_counted.  The kernel spins until every rank has
+ * launched it: every rank must call it the same number of times, in the same order. */
+#define B200DS_P2P_MAX_WORLD 8
+B200DS_API int b200ds_ctx_enable_p2p(b200ds_ctx* ctx, int64_t max_elems);
+B200DS_API int b200ds_allreduce_adam_p2p(b200ds_ctx* ctx, float* params_dev, float* grads_dev,
+                                         float* exp_avg_dev, float* exp_avg_sq_dev, int64_t n, double lr,
+                                         double beta1, double beta2, double eps, int64_t step,
+                                         const uint64_t* step_counter_dev, uintptr_t stream);
+
 /* ---- end-to-end step with HOST buffers (what bench.py's `e2e` times) ---------------
  * One call = train.py:104-115 for one batch: H2D of x,y from (pinned) host memory,
  * forward, loss, backward, all-reduce, Adam (t = step0 + 1), D2H of the loss, and a
@@ -239,7 +258,9 @@ B200DS_API int b200ds_mlp_backward_tc(const void* xq_dev, const void* wq_dev, co
  * kernels when `xq` and `wq` are supplied (non-NULL); everything else the per-stage fp32
  * kernels.  The caller supplies every device buffer in `bufs` (all borrowed):
  *   scratch: b200ds_train_step_scratch_bytes(...) bytes, zeroed once by the caller;
- *   xq / wq: b200ds_tc_xq_bytes(batch) / b200ds_tc_wq_bytes(H) bytes, or NULL for fp32. */
+ *   xq / wq: b200ds_tc_xq_bytes(batch) / b200ds_tc_wq_bytes(H) bytes, or NULL for fp32.
+ * With more than one rank the exchange is ncclAllReduce + the Adam kernel, or the single
+ * peer-memory kernel when b200ds_ctx_enable_p2p has been called with room for the bucket. */
 typedef struct b200ds_step_bufs {
   float* params;  float* grads;  float* exp_avg;  float* exp_avg_sq;   /* flat, length padded to 4 */
   float* x_stage; float* y_stage;          /* [batch*F], [batch] device staging */

@@ -422,6 +422,42 @@ def test_counted_philox_replays_consecutive_draws(lib, cuda_dev):
     assert lib.b200ds_philox_normal_counted(out.data_ptr(), n, seed, 0, None, _st()) == 1
 
 
+@pytest.mark.parametrize("n", [4, 1412, 90116, 400000])
+def test_peer_memory_allreduce_adam_with_one_rank_is_adam(lib, cuda_dev, n):
+    """b200ds_allreduce_adam_p2p at world == 1: the whole publish / wait / read-back protocol runs
+    against this rank's own buffer and must leave exactly what b200ds_adam_step leaves, over
+    several epochs (both halves of the exchange buffer), with the step as an argument and from
+    the device counter; the gradient bucket keeps its (one-rank) sum."""
+    ctx = C.c_void_p()
+    _check(lib, lib.b200ds_ctx_create(0, 0, 1, None, C.byref(ctx)))
+    args = (1e-3, 0.9, 0.999, 1e-8)
+    torch.manual_seed(n)
+    p1 = torch.randn(n, device=cuda_dev); p2 = p1.clone()
+    m1 = torch.zeros(n, device=cuda_dev); v1 = torch.zeros(n, device=cuda_dev)
+    m2 = torch.zeros(n, device=cuda_dev); v2 = torch.zeros(n, device=cuda_dev)
+    g = torch.empty(n, device=cuda_dev)
+    assert lib.b200ds_allreduce_adam_p2p(ctx, p1.data_ptr(), g.data_ptr(), m1.data_ptr(), v1.data_ptr(), n, *args, 1, None, _st()) == 1
+    assert b"enable_p2p" in lib.b200ds_last_error()
+    _check(lib, lib.b200ds_ctx_enable_p2p(ctx, n))
+    assert lib.b200ds_ctx_enable_p2p(ctx, n) == 1                       # once per context
+    ctr = torch.zeros(1, dtype=torch.int64, device=cuda_dev)
+    for step in range(1, 6):
+        g.copy_(torch.randn(n, device=cuda_dev)); g0 = g.clone()
+        if step % 2:
+            _check(lib, lib.b200ds_allreduce_adam_p2p(ctx, p1.data_ptr(), g.data_ptr(), m1.data_ptr(), v1.data_ptr(), n, *args,
+                                                     step, None, _st()))
+        else:
+            ctr.fill_(step)
+            _check(lib, lib.b200ds_allreduce_adam_p2p(ctx, p1.data_ptr(), g.data_ptr(), m1.data_ptr(), v1.data_ptr(), n, *args,
+                                                     0, ctr.data_ptr(), _st()))
+        _check(lib, lib.b200ds_adam_step(p2.data_ptr(), g0.data_ptr(), m2.data_ptr(), v2.data_ptr(), n, *args, step, 1.0, 0, _st()))
+        torch.cuda.synchronize()
+        assert torch.equal(g, g0), step
+        assert torch.equal(p1, p2) and torch.equal(m1, m2) and torch.equal(v1, v2), step
+    assert lib.b200ds_allreduce_adam_p2p(ctx, p1.data_ptr(), g.data_ptr(), m1.data_ptr(), v1.data_ptr(), n + 4, *args, 1, None, _st()) == 1
+    _check(lib, lib.b200ds_ctx_destroy(ctx))
+
+
 def test_single_rank_context_exchange_entry_points_are_no_ops(lib, cuda_dev):
     """world == 1: the all-reduce (whole and in two halves), the broadcast and the barrier return
     at once and leave the bucket alone; the ZeRO-1-style step degenerates to plain Adam."""
