@@ -21,7 +21,9 @@ from b200ds import _lib, comm
 
 def main():
     lib = _lib.load()
-    le = comm.init_distributed()
+    le = comm.read_launch_env()
+    if le.world_size > 1:
+        comm.init_distributed()
     dev = torch.device("cuda", le.local_rank)
     torch.cuda.set_device(dev)
     W, rank = le.world_size, le.rank
@@ -56,15 +58,19 @@ def main():
             torch.cuda.synchronize()
             worst = max(worst, float((ga - gb).abs().max() / ga.abs().max()))
         perr = float((pa - pb).abs().max() / pa.abs().max())
-        gathered = [torch.zeros_like(pb) for _ in range(W)]
-        dist.all_gather(gathered, pb)
-        same = all(torch.equal(gathered[0], t) for t in gathered)
+        same = True
+        if W > 1:
+            gathered = [torch.zeros_like(pb) for _ in range(W)]
+            dist.all_gather(gathered, pb)
+            same = all(torch.equal(gathered[0], t) for t in gathered)
         good = perr <= 1e-5 and worst <= 1e-5 and same
         ok = ok and good
         # time per call (eager launches, CUDA events, after warm-up; every rank runs the same count)
         reps = 200
         e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
-        dist.barrier(); torch.cuda.synchronize()
+        if W > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
         e0.record()
         for i in range(reps):
             lib.b200ds_allreduce_bucket(ctx, ga.data_ptr(), n, st)
@@ -78,9 +84,11 @@ def main():
             print(f"p2p_check n={n} world={W}: bucket sum rel diff {worst:.1e}, param rel diff {perr:.1e}, replicas bit-equal {same}"
                   f" -> {'OK' if good else 'FAIL'};  NCCL all-reduce + Adam {1e3 * e0.elapsed_time(e1) / reps:.1f} us/call,"
                   f" peer-memory kernel {1e3 * e1.elapsed_time(e2) / reps:.1f} us/call", flush=True)
-    dist.barrier()
+    if W > 1:
+        dist.barrier()
     _lib.check(lib.b200ds_ctx_destroy(ctx))
-    dist.destroy_process_group()
+    if W > 1:
+        dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 
 
