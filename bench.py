@@ -212,7 +212,7 @@ class WideStep:
         self.p2p = world > 1 and not os.environ.get("B200DS_BENCH_NCCL")
         if self.p2p:
             _lib.check(lib.b200ds_ctx_enable_p2p(ctx, self.Ppad))
-            self.side = torch.cuda.Stream(device=dev)
+        self.side = torch.cuda.Stream(device=dev)
 
     def step(self, st, ev_pair=None):
         lib, chk = self.lib, self._lib.check
@@ -220,17 +220,15 @@ class WideStep:
         # the draw index is the device step counter (incremented by the loss kernel), so the same
         # launch sequence can be replayed from a CUDA graph and still get a fresh batch each step
         if self.tc:
-            if not self.primed:      # batch 0; later batches are drawn beside the previous step's all-reduce
+            if not self.primed:      # batch 0 and the first weight pack; later ones are made at the end of the previous step
                 self.gen_next(st)
+                self.pack(st)
                 self.primed = True
-        else:
-            chk(lib.b200ds_philox_normal_counted(self.x.data_ptr(), B * F, self.seed, 0, self.counter.data_ptr(), st))
-            chk(lib.b200ds_label_rule(self.x.data_ptr(), self.y.data_ptr(), B, F, st))
-        if self.tc:
-            chk(lib.b200ds_pack_params_bf16(self.params.data_ptr(), F, H, self.wq.data_ptr(), st))
             chk(lib.b200ds_mlp_forward_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.params.data_ptr(), B, F, H,
                                           self.logits.data_ptr(), st))
         else:
+            chk(lib.b200ds_philox_normal_counted(self.x.data_ptr(), B * F, self.seed, 0, self.counter.data_ptr(), st))
+            chk(lib.b200ds_label_rule(self.x.data_ptr(), self.y.data_ptr(), B, F, st))
             chk(lib.b200ds_mlp_forward_f32(self.params.data_ptr(), self.x.data_ptr(), B, F, H, self.logits.data_ptr(), st))
         chk(lib.b200ds_bce_loss_grad(self.logits.data_ptr(), self.y.data_ptr(), B, self.loss.data_ptr(), self.dz.data_ptr(),
                                      self.counter.data_ptr(), self.bce_sc.data_ptr(), self.bce_sc.numel(), st))
@@ -244,23 +242,29 @@ class WideStep:
                                             self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
         if ev_pair:
             ev_pair[1].record()
-        if self.p2p:
-            # the exchange kernel (mostly waiting on NVLink round trips, at most one CTA per SM) runs on a
-            # side stream while the next batch is generated here; both are done before the next step starts
+        # ---- exchange + Adam, and (bf16) the next step's inputs: the next batch does not need this step's
+        # gradients, so it is generated on the main stream while the exchange, Adam and the new weight pack
+        # run on a side stream; both are done before the next step starts
+        if self.tc and self.p2p:
+            # the exchange kernel mostly waits on NVLink round trips (at most one CTA per SM): it overlaps with
+            # the generator.  (With one rank the same fork was measured and gains nothing: the generator fills
+            # every thread slot, so Adam and the pack only start when it drains.)
             main = torch.cuda.current_stream()
             fork = torch.cuda.Event(); fork.record(main)
             self.side.wait_event(fork)
+            sst = self.side.cuda_stream
             chk(lib.b200ds_allreduce_adam_p2p(self.ctx, self.params.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),
-                                              self.v.data_ptr(), self.Ppad, LR, 0.9, 0.999, 1e-8, 0, self.counter.data_ptr(),
-                                              self.side.cuda_stream))
+                                              self.v.data_ptr(), self.Ppad, LR, 0.9, 0.999, 1e-8, 0, self.counter.data_ptr(), sst))
+            self.pack(sst)
             join = torch.cuda.Event(); join.record(self.side)
-            if self.tc:
-                self.gen_next(st)
+            self.gen_next(st)
             main.wait_event(join)
             return
-        if self.tc:
-            # the next batch does not need this step's gradients: it is generated on the main stream
-            # while the all-reduce runs on the context's side stream (the backward is done with xq)
+        if self.p2p:        # fp32 kernels
+            chk(lib.b200ds_allreduce_adam_p2p(self.ctx, self.params.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(),
+                                              self.v.data_ptr(), self.Ppad, LR, 0.9, 0.999, 1e-8, 0, self.counter.data_ptr(), st))
+            return
+        if self.tc:         # NCCL arm: the all-reduce on the context's side stream beside the generator
             chk(lib.b200ds_allreduce_bucket_begin(self.ctx, self.grads.data_ptr(), self.P, st))
             self.gen_next(st)
             chk(lib.b200ds_allreduce_bucket_end(self.ctx, st))
@@ -269,6 +273,12 @@ class WideStep:
         chk(lib.b200ds_adam_step_counted(self.params.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
                                          self.Ppad, LR, 0.9, 0.999, 1e-8, self.counter.data_ptr(),
                                          1.0 / self.world, 0, st))
+        if self.tc:
+            self.pack(st)
+
+    def pack(self, st):
+        """bf16 operand pack of the current W1 / b1 (+ the partials of v = w1q^T w2) for the next forward."""
+        self._lib.check(self.lib.b200ds_pack_params_bf16(self.params.data_ptr(), self.F, self.H, self.wq.data_ptr(), st))
 
     def gen_next(self, st):
         """Batch number *counter of the Philox stream (the loss kernel has already counted this
