@@ -211,7 +211,16 @@ class WideStep:
         # fixed summation order); B200DS_BENCH_NCCL=1 selects ncclAllReduce + the Adam kernel instead
         self.p2p = world > 1 and not os.environ.get("B200DS_BENCH_NCCL")
         if self.p2p:
-            _lib.check(lib.b200ds_ctx_enable_p2p(ctx, self.Ppad))
+            # collective; if any rank cannot map its peers (no peer access on this box) every rank takes the NCCL exchange
+            import torch.distributed as dist
+            rc = lib.b200ds_ctx_enable_p2p(ctx, self.Ppad)
+            okf = torch.tensor([1.0 if rc == 0 else 0.0], device=dev)
+            dist.all_reduce(okf, op=dist.ReduceOp.MIN)
+            if float(okf) < 1.0:
+                if rank == 0:
+                    print("bench: peer-memory exchange unavailable (%s); using ncclAllReduce + Adam"
+                          % lib.b200ds_last_error().decode("utf-8", "replace"), file=sys.stderr, flush=True)
+                self.p2p = False
         self.side = torch.cuda.Stream(device=dev)
 
     def step(self, st, ev_pair=None):

@@ -170,16 +170,28 @@ int b200ds_ctx_enable_p2p(b200ds_ctx* ctx, int64_t max_elems) {
     P2PHandles all[B200DS_P2P_MAX_WORLD];
     B200_CUDA(cudaMemcpy(all, gather, sizeof(P2PHandles) * (size_t)W, cudaMemcpyDeviceToHost));
     B200_CUDA(cudaFree(gather));
-    for (int w = 0; w < W; ++w) {
+    // A rank that cannot map a peer (no peer access between the two devices, device not visible to
+    // this process) must still reach the barrier below, or the others would wait for it forever.
+    int map_rc = B200DS_OK;
+    for (int w = 0; w < W && map_rc == B200DS_OK; ++w) {
       if (w == ctx->rank) continue;
       void* px = nullptr; void* pf = nullptr;
-      B200_CUDA(cudaIpcOpenMemHandle(&px, all[w].xchg, cudaIpcMemLazyEnablePeerAccess));
-      B200_CUDA(cudaIpcOpenMemHandle(&pf, all[w].flags, cudaIpcMemLazyEnablePeerAccess));
-      ctx->p2p_xchg[w] = reinterpret_cast<float*>(px);
-      ctx->p2p_flags[w] = reinterpret_cast<unsigned long long*>(pf);
+      cudaError_t e = cudaIpcOpenMemHandle(&px, all[w].xchg, cudaIpcMemLazyEnablePeerAccess);
+      if (e == cudaSuccess) {
+        ctx->p2p_xchg[w] = reinterpret_cast<float*>(px);
+        e = cudaIpcOpenMemHandle(&pf, all[w].flags, cudaIpcMemLazyEnablePeerAccess);
+      }
+      if (e == cudaSuccess) {
+        ctx->p2p_flags[w] = reinterpret_cast<unsigned long long*>(pf);
+      } else {
+        cudaGetLastError();
+        set_error("ctx_enable_p2p: cannot map rank %d's exchange buffer: %s", w, cudaGetErrorString(e));
+        map_rc = B200DS_ERR_CUDA;
+      }
     }
     // nobody may publish before every rank has opened every mapping and zeroed its words
     int rc = b200ds_barrier(ctx);
+    if (map_rc) return map_rc;
     if (rc) return rc;
   }
   ctx->p2p_cap = cap;
