@@ -204,9 +204,9 @@ class WideStep:
             self.xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=dev)
             self.wq = torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=dev)
             self.bwd_sc = torch.zeros(max(256, lib.b200ds_mlp_backward_tc_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
-            self.dominant = dict(name="mlp_bwd_tc_kernel", bound="tensor")
-        # bf16: gen_batch, pack_w1, forward, loss, backward, finish, adam; fp32: philox, label, forward, loss, backward, finish, adam
-        self.launches_per_step = 7
+            self.dominant = dict(name="mlp_bwd_tc_kernel<LOSS> (+finish)", bound="tensor")
+        # bf16: gen_batch, pack_w1, forward, loss+backward, finish, adam; fp32: philox, label, forward, loss, backward, finish, adam
+        self.launches_per_step = 6 if precision == "bf16" else 7
         # W > 1: gradient exchange + Adam as one peer-memory kernel (NVLink loads of the peers' buckets,
         # fixed summation order); B200DS_BENCH_NCCL=1 selects ncclAllReduce + the Adam kernel instead
         self.p2p = world > 1 and not os.environ.get("B200DS_BENCH_NCCL")
@@ -239,14 +239,17 @@ class WideStep:
             chk(lib.b200ds_philox_normal_counted(self.x.data_ptr(), B * F, self.seed, 0, self.counter.data_ptr(), st))
             chk(lib.b200ds_label_rule(self.x.data_ptr(), self.y.data_ptr(), B, F, st))
             chk(lib.b200ds_mlp_forward_f32(self.params.data_ptr(), self.x.data_ptr(), B, F, H, self.logits.data_ptr(), st))
-        chk(lib.b200ds_bce_loss_grad(self.logits.data_ptr(), self.y.data_ptr(), B, self.loss.data_ptr(), self.dz.data_ptr(),
-                                     self.counter.data_ptr(), self.bce_sc.data_ptr(), self.bce_sc.numel(), st))
         if ev_pair:
             ev_pair[0].record()
         if self.tc:
-            chk(lib.b200ds_mlp_backward_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.params.data_ptr(), self.dz.data_ptr(),
-                                           B, F, H, self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
+            # criterion + backward in one pass: four warps of the backward kernel form dlogits from the logits and labels
+            chk(lib.b200ds_mlp_loss_backward_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.params.data_ptr(),
+                                                self.logits.data_ptr(), self.y.data_ptr(), B, F, H, self.loss.data_ptr(),
+                                                self.grads.data_ptr(), self.counter.data_ptr(), self.bwd_sc.data_ptr(),
+                                                self.bwd_sc.numel(), st))
         else:
+            chk(lib.b200ds_bce_loss_grad(self.logits.data_ptr(), self.y.data_ptr(), B, self.loss.data_ptr(), self.dz.data_ptr(),
+                                         self.counter.data_ptr(), self.bce_sc.data_ptr(), self.bce_sc.numel(), st))
             chk(lib.b200ds_mlp_backward_f32(self.params.data_ptr(), self.x.data_ptr(), self.dz.data_ptr(), B, F, H,
                                             self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
         if ev_pair:

@@ -52,11 +52,11 @@ static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const flo
   } else {
     if ((rc = b200ds_mlp_forward_f32(b->params, x_dev, batch, n_features, hidden, b->logits, stream))) return rc;
   }
-  if ((rc = b200ds_bce_loss_grad(b->logits, y_dev, batch, b->loss, b->dlogits, nullptr, sc, bce_bytes, stream))) return rc;
-  if (use_tc) {
-    if ((rc = b200ds_mlp_backward_tc(b->xq, b->wq, b->params, b->dlogits, batch, n_features, hidden, b->grads,
-                                     sc + bce_bytes, b->scratch_bytes - bce_bytes, stream))) return rc;
+  if (use_tc) {       // criterion + backward in one pass (dlogits is not materialised on this path)
+    if ((rc = b200ds_mlp_loss_backward_tc(b->xq, b->wq, b->params, b->logits, y_dev, batch, n_features, hidden, b->loss,
+                                          b->grads, nullptr, sc + bce_bytes, b->scratch_bytes - bce_bytes, stream))) return rc;
   } else {
+    if ((rc = b200ds_bce_loss_grad(b->logits, y_dev, batch, b->loss, b->dlogits, nullptr, sc, bce_bytes, stream))) return rc;
     if ((rc = b200ds_mlp_backward_f32(b->params, x_dev, b->dlogits, batch, n_features, hidden, b->grads,
                                       sc + bce_bytes, b->scratch_bytes - bce_bytes, stream))) return rc;
   }

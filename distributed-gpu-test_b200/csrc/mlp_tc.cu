@@ -389,18 +389,27 @@ constexpr int kBwdRing = 3;               // D1T accumulators: 3 x 128 columns (
 constexpr int kBwdNB = 4;                 // n blocks per CTA: S accumulators 4 x 32 columns (cols 384..511)
 constexpr int kBwdThreads = 32 * 12;      // 0-7 epilogue (two groups), 8 TMA + dz stager, 9 MMA1, 10-11 MMA2 (n block parity);
                                           // issuers at the highest warp ids, see the forward kernel
+constexpr int kBwdLossThreads = 32 * 16;  // fused loss: warps 12-15 form dz (one row of the tile per thread) instead of warp 8
 
 struct BwdSmem {
   uint32_t dzs[kBwdXStages][64];          // dz of the tile as bf16x2 pairs
   uint64_t w_bar, x_full[kBwdXStages], x_free[kBwdXStages], dz_full[kBwdXStages];
   uint64_t d1_full[kBwdRing], d1_free[kBwdRing], a_ready[kBwdRing], s_full;
   uint32_t tmem_slot;
+  float lred[4][2];                       // fused loss: per-warp sums of dz and of the loss terms
 };
 
-__global__ void __launch_bounds__(kBwdThreads, 1)
+// LOSS: the loss kernel is folded in -- `dz` holds the LOGITS; four extra warps form
+// dz[b] = (sigmoid(z) - y) / B for the tile (one row per thread, the arithmetic of
+// bce_loss_grad_kernel: the W1 / b1 / W2 gradients are bit-identical to the two-kernel path), and
+// in the CTAs of group 0 they also sum the loss terms into loss_part[split]; the finish pass adds
+// those up.  dlogits never reaches HBM.
+template <bool LOSS>
+__global__ void __launch_bounds__(kBwdLossThreads, 1)
 mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __restrict__ w1q,
-                  const float* __restrict__ dz, float* __restrict__ partial /* [splits][H][32] */,
-                  float* __restrict__ db2_part /* [splits] */, int n_btiles, int hidden, int nb, int n_groups, int n_splits) {
+                  const float* __restrict__ dz, const float* __restrict__ ylab, float fbatch,
+                  float* __restrict__ partial /* [splits][H][32] */, float* __restrict__ db2_part /* [splits] */,
+                  float* __restrict__ loss_part /* [splits] */, int n_btiles, int hidden, int nb, int n_groups, int n_splits) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int group = blockIdx.x % n_groups, split = blockIdx.x / n_groups;
@@ -414,7 +423,7 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
   if (threadIdx.x == 0) {
     mbar_init(&sh->w_bar, 1);
     const uint32_t n_issuers = nb < 2 ? 1u : 2u;     // MMA2 issuing threads that commit per tile
-    for (int i = 0; i < kBwdXStages; ++i) { mbar_init(&sh->x_full[i], 1); mbar_init(&sh->x_free[i], n_issuers); mbar_init(&sh->dz_full[i], 1); }
+    for (int i = 0; i < kBwdXStages; ++i) { mbar_init(&sh->x_full[i], 1); mbar_init(&sh->x_free[i], n_issuers); mbar_init(&sh->dz_full[i], LOSS ? 4 : 1); }
     for (int i = 0; i < kBwdRing; ++i) { mbar_init(&sh->d1_full[i], 1); mbar_init(&sh->d1_free[i], 1); mbar_init(&sh->a_ready[i], 4); }
     mbar_init(&sh->s_full, n_issuers);
     mbar_fence_init();
@@ -446,18 +455,52 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         mbar_arrive_expect_tx(&sh->x_full[s], kTileBytes);
         tma_load_1d(xs + s * kTileBytes, xq + (size_t)t * kTileBytes, kTileBytes, &sh->x_full[s]);
       }
-      const float4 d = d0;
-      d0 = d1; d1 = d2; d2 = dz_tile(t + 3);
-      dsum += (d.x + d.y) + (d.z + d.w);
-      __nv_bfloat162 p0 = __floats2bfloat162_rn(d.x, d.y), p1 = __floats2bfloat162_rn(d.z, d.w);
-      sh->dzs[s][lane * 2 + 0] = *reinterpret_cast<uint32_t*>(&p0);
-      sh->dzs[s][lane * 2 + 1] = *reinterpret_cast<uint32_t*>(&p1);
+      if (!LOSS) {
+        const float4 d = d0;
+        d0 = d1; d1 = d2; d2 = dz_tile(t + 3);
+        dsum += (d.x + d.y) + (d.z + d.w);
+        __nv_bfloat162 p0 = __floats2bfloat162_rn(d.x, d.y), p1 = __floats2bfloat162_rn(d.z, d.w);
+        sh->dzs[s][lane * 2 + 0] = *reinterpret_cast<uint32_t*>(&p0);
+        sh->dzs[s][lane * 2 + 1] = *reinterpret_cast<uint32_t*>(&p1);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sh->dz_full[s]);
+      }
+      if (++s == kBwdXStages) { s = 0; ph ^= 1; }
+    }
+    if (!LOSS) {
+      dsum = warp_sum(dsum);       // this split's share of db2 = sum_b dz[b]
+      if (group == 0 && lane == 0) db2_part[split] = dsum;
+    }
+  } else if (warp >= 12) {
+    // ===== fused loss (LOSS only; the launch has no such warps otherwise): thread = row of the tile =====
+    const int r = (warp - 12) * 32 + lane;
+    auto ld = [&](const float* src, int t) { return t < t_end ? __ldg(src + (size_t)t * kTileRows + r) : 0.f; };
+    // logits and labels are read three tiles ahead (see the dz loads of the plain path)
+    float z0 = ld(dz, t_begin), z1 = ld(dz, t_begin + 1), z2 = ld(dz, t_begin + 2);
+    float y0 = ld(ylab, t_begin), y1 = ld(ylab, t_begin + 1), y2 = ld(ylab, t_begin + 2);
+    float dsum = 0.f, lsum = 0.f;
+    int s = 0; uint32_t ph = 0;
+    for (int t = t_begin; t < t_end; ++t) {
+      const float z = z0, y = y0;
+      z0 = z1; z1 = z2; z2 = ld(dz, t + 3);
+      y0 = y1; y1 = y2; y2 = ld(ylab, t + 3);
+      const float d = bce_grad(z, y, fbatch);
+      dsum += d;
+      if (group == 0) lsum += bce_term(z, y);
+      mbar_wait(&sh->x_free[s], ph ^ 1);                  // the stage's previous tile is done with dzs[s]
+      reinterpret_cast<__nv_bfloat16*>(sh->dzs[s])[r] = __float2bfloat16(d);
       __syncwarp();
       if (lane == 0) mbar_arrive(&sh->dz_full[s]);
       if (++s == kBwdXStages) { s = 0; ph ^= 1; }
     }
-    dsum = warp_sum(dsum);       // this split's share of db2 = sum_b dz[b]
-    if (group == 0 && lane == 0) db2_part[split] = dsum;
+    dsum = warp_sum(dsum);
+    lsum = warp_sum(lsum);
+    if (lane == 0) { sh->lred[warp - 12][0] = dsum; sh->lred[warp - 12][1] = lsum; }
+    asm volatile("bar.sync 2, 128;" ::: "memory");
+    if (group == 0 && warp == 12 && lane == 0) {           // fixed order over the four warps
+      db2_part[split] = (sh->lred[0][0] + sh->lred[1][0]) + (sh->lred[2][0] + sh->lred[3][0]);
+      loss_part[split] = (sh->lred[0][1] + sh->lred[1][1]) + (sh->lred[2][1] + sh->lred[3][1]);
+    }
   } else if (warp == 9) {
     // ===== MMA1 issuer: D1T[ring] = w1_block . x_tile^T (lanes = n, columns = b) =====
     {
@@ -602,7 +645,9 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
 // grads from S: one warp per hidden unit n, lane = k; split partials summed in split order
 __global__ void __launch_bounds__(256)
 mlp_bwd_tc_finish(const float* __restrict__ partial, const float* __restrict__ db2_part, int n_splits,
-                  const float* __restrict__ params, Layout L, float* __restrict__ grads) {
+                  const float* __restrict__ params, Layout L, float* __restrict__ grads,
+                  const float* __restrict__ loss_part, double inv_batch, float* __restrict__ loss_out,
+                  unsigned long long* __restrict__ step_counter) {
   const int lane = threadIdx.x & 31;
   const int wpb = blockDim.x >> 5;
   const size_t stride = (size_t)L.H * 32;
@@ -637,6 +682,12 @@ mlp_bwd_tc_finish(const float* __restrict__ partial, const float* __restrict__ d
     float t = 0.f;
     for (int sp = 0; sp < n_splits; ++sp) t += db2_part[sp];
     grads[L.off_b2()] = t;
+    if (loss_part) {             // fused loss: mean over the batch, split partials summed in split order in double
+      double ls = 0.0;
+      for (int sp = 0; sp < n_splits; ++sp) ls += (double)loss_part[sp];
+      *loss_out = (float)(ls * inv_batch);
+      if (step_counter) *step_counter += 1ull;
+    }
   }
 }
 
@@ -786,42 +837,69 @@ size_t b200ds_mlp_backward_tc_scratch_bytes(int64_t batch, int n_features, int h
   if (!tc_shape_ok(batch, n_features, hidden)) return 0;
   BwdPlan bp;
   bwd_plan(batch, hidden, &bp);
-  return (size_t)bp.splits * hidden * 32 * sizeof(float) + (size_t)bp.splits * sizeof(float);
+  return (size_t)bp.splits * hidden * 32 * sizeof(float) + 2 * (size_t)bp.splits * sizeof(float);
 }
 
-int b200ds_mlp_backward_tc(const void* xq_dev, const void* wq_dev, const float* params_dev,
-                           const float* dlogits_dev, int64_t batch, int n_features, int hidden,
-                           float* grads_dev, void* scratch_dev, size_t scratch_bytes, uintptr_t stream) {
+static int launch_backward_tc(const char* who, const void* xq_dev, const void* wq_dev, const float* params_dev,
+                              const float* dz_or_logits_dev, const float* y_dev, float* loss_dev, uint64_t* step_counter_dev,
+                              int64_t batch, int n_features, int hidden, float* grads_dev, void* scratch_dev,
+                              size_t scratch_bytes, uintptr_t stream) {
+  const bool fused = y_dev != nullptr;
   B200_REQUIRE(tc_shape_ok(batch, n_features, hidden),
-               "mlp_backward_tc: needs F <= %d, H %% 128 == 0, batch %% 128 == 0 (got B=%lld F=%d H=%d)", KP - 2,
+               "%s: needs F <= %d, H %% 128 == 0, batch %% 128 == 0 (got B=%lld F=%d H=%d)", who, KP - 2,
                (long long)batch, n_features, hidden);
-  B200_REQUIRE(xq_dev && wq_dev && params_dev && dlogits_dev && grads_dev, "mlp_backward_tc: null pointer");
-  B200_REQUIRE((((uintptr_t)dlogits_dev) & 15) == 0, "mlp_backward_tc: dlogits must be 16-byte aligned");
+  B200_REQUIRE(xq_dev && wq_dev && params_dev && dz_or_logits_dev && grads_dev, "%s: null pointer", who);
+  B200_REQUIRE((((uintptr_t)dz_or_logits_dev) & 15) == 0 && (((uintptr_t)y_dev) & 15) == 0,
+               "%s: logits / dlogits / labels must be 16-byte aligned", who);
   BwdPlan bp;
   bwd_plan(batch, hidden, &bp);
-  size_t need = (size_t)bp.splits * hidden * 32 * sizeof(float) + (size_t)bp.splits * sizeof(float);
-  B200_REQUIRE(scratch_dev && scratch_bytes >= need, "mlp_backward_tc: scratch too small (%zu < %zu)", scratch_bytes, need);
+  size_t need = b200ds_mlp_backward_tc_scratch_bytes(batch, n_features, hidden);
+  B200_REQUIRE(scratch_dev && scratch_bytes >= need, "%s: scratch too small (%zu < %zu)", who, scratch_bytes, need);
   Layout L{n_features, hidden};
   cudaStream_t st = as_stream(stream);
   static bool attr_set[64];
   int dev = 0;
   B200_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
-    B200_CUDA(cudaFuncSetAttribute(mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    B200_CUDA(cudaFuncSetAttribute(mlp_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    B200_CUDA(cudaFuncSetAttribute(mlp_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set[dev & 63] = true;
   }
   const unsigned char* w1q = reinterpret_cast<const unsigned char*>(wq_dev);
   float* db2_part = reinterpret_cast<float*>(scratch_dev) + (size_t)bp.splits * hidden * 32;
-  mlp_bwd_tc_kernel<<<bp.groups * bp.splits, kBwdThreads, bp.smem, st>>>(
-      reinterpret_cast<const unsigned char*>(xq_dev), w1q, dlogits_dev, reinterpret_cast<float*>(scratch_dev), db2_part,
-      bp.n_btiles, hidden, bp.nb, bp.groups, bp.splits);
+  float* loss_part = db2_part + bp.splits;
+  if (fused)
+    mlp_bwd_tc_kernel<true><<<bp.groups * bp.splits, kBwdLossThreads, bp.smem, st>>>(
+        reinterpret_cast<const unsigned char*>(xq_dev), w1q, dz_or_logits_dev, y_dev, (float)batch,
+        reinterpret_cast<float*>(scratch_dev), db2_part, loss_part, bp.n_btiles, hidden, bp.nb, bp.groups, bp.splits);
+  else
+    mlp_bwd_tc_kernel<false><<<bp.groups * bp.splits, kBwdThreads, bp.smem, st>>>(
+        reinterpret_cast<const unsigned char*>(xq_dev), w1q, dz_or_logits_dev, nullptr, (float)batch,
+        reinterpret_cast<float*>(scratch_dev), db2_part, loss_part, bp.n_btiles, hidden, bp.nb, bp.groups, bp.splits);
   B200_LAUNCH_CHECK();
   int fgrid = (hidden + 7) / 8;
   if (fgrid > sm_count() * 8) fgrid = sm_count() * 8;
   mlp_bwd_tc_finish<<<fgrid, 256, 0, st>>>(reinterpret_cast<const float*>(scratch_dev), db2_part, bp.splits, params_dev, L,
-                                           grads_dev);
+                                           grads_dev, fused ? loss_part : nullptr, 1.0 / (double)batch, loss_dev,
+                                           reinterpret_cast<unsigned long long*>(step_counter_dev));
   B200_LAUNCH_CHECK();
   return B200DS_OK;
+}
+
+int b200ds_mlp_backward_tc(const void* xq_dev, const void* wq_dev, const float* params_dev,
+                           const float* dlogits_dev, int64_t batch, int n_features, int hidden,
+                           float* grads_dev, void* scratch_dev, size_t scratch_bytes, uintptr_t stream) {
+  return launch_backward_tc("mlp_backward_tc", xq_dev, wq_dev, params_dev, dlogits_dev, nullptr, nullptr, nullptr, batch,
+                            n_features, hidden, grads_dev, scratch_dev, scratch_bytes, stream);
+}
+
+int b200ds_mlp_loss_backward_tc(const void* xq_dev, const void* wq_dev, const float* params_dev,
+                                const float* logits_dev, const float* y_dev, int64_t batch, int n_features, int hidden,
+                                float* loss_dev, float* grads_dev, uint64_t* step_counter_dev, void* scratch_dev,
+                                size_t scratch_bytes, uintptr_t stream) {
+  B200_REQUIRE(y_dev && loss_dev, "mlp_loss_backward_tc: null pointer");
+  return launch_backward_tc("mlp_loss_backward_tc", xq_dev, wq_dev, params_dev, logits_dev, y_dev, loss_dev, step_counter_dev,
+                            batch, n_features, hidden, grads_dev, scratch_dev, scratch_bytes, stream);
 }
 
 }  // extern "C"

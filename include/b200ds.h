@@ -230,6 +230,20 @@ B200DS_API int b200ds_mlp_backward_tc(const void* xq_dev, const void* wq_dev, co
                                       float* grads_dev, void* scratch_dev, size_t scratch_bytes,
                                       uintptr_t stream);
 
+/* criterion(logits, y) and model_engine.backward(loss) up to the all-reduce (train.py:112-113) as
+ * ONE pass: four extra warps of the backward kernel form dlogits = (sigmoid(z) - y) / B from the
+ * logits and labels (the arithmetic of b200ds_bce_loss_grad: the W1 / b1 / W2 gradients are
+ * bit-identical to that call followed by b200ds_mlp_backward_tc; db2 and the loss differ by
+ * summation order only) and sum the loss terms on the side; dlogits is never written.
+ * loss_dev receives the batch mean; step_counter_dev (NULL allowed) is incremented as
+ * b200ds_bce_loss_grad does.  Scratch: b200ds_mlp_backward_tc_scratch_bytes.  logits and labels
+ * 16-byte aligned. */
+B200DS_API int b200ds_mlp_loss_backward_tc(const void* xq_dev, const void* wq_dev, const float* params_dev,
+                                           const float* logits_dev, const float* y_dev, int64_t batch,
+                                           int n_features, int hidden, float* loss_dev, float* grads_dev,
+                                           uint64_t* step_counter_dev, void* scratch_dev, size_t scratch_bytes,
+                                           uintptr_t stream);
+
 /* ---- gradient exchange + optimizer step over NVLink peer memory ---------------------
  * model_engine.backward's all-reduce and model_engine.step()'s Adam (train.py:113-114) as ONE
  * kernel: every rank publishes its gradient bucket in a buffer its peers have mapped (CUDA

@@ -181,6 +181,45 @@ def test_host_buffer_step_tc_path(lib, cuda_dev):
     _chk(lib.b200ds_ctx_destroy(ctx))
 
 
+@pytest.mark.parametrize("B,F,H", [(128, 20, 128), (1024, 20, 384), (65536, 20, 4096), (384, 7, 640)])
+def test_fused_loss_backward_equals_loss_then_backward(lib, cuda_dev, B, F, H):
+    """b200ds_mlp_loss_backward_tc == b200ds_bce_loss_grad + b200ds_mlp_backward_tc: W1 / b1 / W2
+    gradients bit for bit (the same dlogits arithmetic inside the kernel), db2 and the loss to fp32
+    round-off (another summation order), step counter incremented once; twice in a row."""
+    torch.manual_seed(B + H)
+    p = ora.init_params(F, H)
+    flat = ora.flatten(p)
+    P = flat.numel(); Ppad = (P + 3) // 4 * 4
+    params = torch.zeros(Ppad, device=cuda_dev); params[:P] = flat.to(cuda_dev)
+    x = torch.randn(B, F, device=cuda_dev)
+    y = (x[:, : max(1, F // 2)].sum(dim=1) > 0).float().contiguous()
+    xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=cuda_dev)
+    wq = torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=cuda_dev)
+    z = torch.empty(B, device=cuda_dev)
+    _chk(lib.b200ds_pack_x_bf16(x.data_ptr(), B, F, xq.data_ptr(), _st()))
+    _chk(lib.b200ds_pack_params_bf16(params.data_ptr(), F, H, wq.data_ptr(), _st()))
+    _chk(lib.b200ds_mlp_forward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), B, F, H, z.data_ptr(), _st()))
+    sc = torch.zeros(lib.b200ds_mlp_backward_tc_scratch_bytes(B, F, H), dtype=torch.uint8, device=cuda_dev)
+    bsc = torch.zeros(lib.b200ds_bce_scratch_bytes(B), dtype=torch.uint8, device=cuda_dev)
+    dz = torch.empty(B, device=cuda_dev)
+    la, lb = torch.zeros(1, device=cuda_dev), torch.zeros(1, device=cuda_dev)
+    ga, gb = torch.zeros(Ppad, device=cuda_dev), torch.full((Ppad,), float("nan"), device=cuda_dev)
+    ca, cb = torch.zeros(1, dtype=torch.int64, device=cuda_dev), torch.zeros(1, dtype=torch.int64, device=cuda_dev)
+    _chk(lib.b200ds_bce_loss_grad(z.data_ptr(), y.data_ptr(), B, la.data_ptr(), dz.data_ptr(), ca.data_ptr(), bsc.data_ptr(),
+                                  bsc.numel(), _st()))
+    _chk(lib.b200ds_mlp_backward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), dz.data_ptr(), B, F, H, ga.data_ptr(),
+                                    sc.data_ptr(), sc.numel(), _st()))
+    for rep in range(2):
+        gb.fill_(float("nan"))
+        _chk(lib.b200ds_mlp_loss_backward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), z.data_ptr(), y.data_ptr(), B, F, H,
+                                             lb.data_ptr(), gb.data_ptr(), cb.data_ptr(), sc.data_ptr(), sc.numel(), _st()))
+        torch.cuda.synchronize()
+        assert torch.equal(ga[:P - 1], gb[:P - 1]), rep
+        assert abs(float(ga[P - 1]) - float(gb[P - 1])) <= 1e-5 * max(1e-30, abs(float(ga[P - 1]))) + 1e-9, rep
+        assert abs(float(la) - float(lb)) <= 1e-5 * abs(float(la)), rep
+    assert int(ca) == 1 and int(cb) == 2
+
+
 def _host_step_state(lib, dev, B, F, H, stage_batches):
     from b200ds import _lib
     torch.manual_seed(11)
