@@ -206,14 +206,16 @@ class WideStep:
             self.bwd_sc = torch.zeros(max(256, lib.b200ds_mlp_backward_tc_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
             self.dominant = dict(name="mlp_bwd_tc_kernel<LOSS> (+finish)", bound="tensor")
         # bf16: gen_batch, pack_w1, forward, loss+backward, finish, adam; fp32: philox, label, forward, loss, backward, finish, adam
-        self.launches_per_step = 6 if precision == "bf16" else 7
+        self.launches_per_step = 6 if precision == "bf16" else 7          # 4 with the fused update (set below)
         # W > 1: gradient exchange + Adam as one peer-memory kernel (NVLink loads of the peers' buckets,
         # fixed summation order); B200DS_BENCH_NCCL=1 selects ncclAllReduce + the Adam kernel instead
         self.p2p = world > 1 and not os.environ.get("B200DS_BENCH_NCCL")
+        # bf16: finish + exchange + Adam + pack as one kernel (B200DS_BENCH_UNFUSED=1: the separate kernels)
+        self.fused_update = self.tc and not os.environ.get("B200DS_BENCH_UNFUSED") and (world == 1 or self.p2p)
         if self.p2p:
             # collective; if any rank cannot map its peers (no peer access on this box) every rank takes the NCCL exchange
             import torch.distributed as dist
-            rc = lib.b200ds_ctx_enable_p2p(ctx, self.Ppad)
+            rc = lib.b200ds_ctx_enable_p2p(ctx, max(self.Ppad, lib.b200ds_update_tc_exchange_elems(H) if self.tc else 0))
             okf = torch.tensor([1.0 if rc == 0 else 0.0], device=dev)
             dist.all_reduce(okf, op=dist.ReduceOp.MIN)
             if float(okf) < 1.0:
@@ -221,7 +223,15 @@ class WideStep:
                     print("bench: peer-memory exchange unavailable (%s); using ncclAllReduce + Adam"
                           % lib.b200ds_last_error().decode("utf-8", "replace"), file=sys.stderr, flush=True)
                 self.p2p = False
+                self.fused_update = False
         self.side = torch.cuda.Stream(device=dev)
+
+    @property
+    def launches(self):
+        """kernels of this library launched per step"""
+        if not self.tc:
+            return 7                      # philox, label, forward, loss, backward, finish, adam
+        return 4 if self.fused_update else 6   # gen_batch, forward, loss+backward, update | ... finish, adam, pack_w1
 
     def step(self, st, ev_pair=None):
         lib, chk = self.lib, self._lib.check
@@ -241,8 +251,13 @@ class WideStep:
             chk(lib.b200ds_mlp_forward_f32(self.params.data_ptr(), self.x.data_ptr(), B, F, H, self.logits.data_ptr(), st))
         if ev_pair:
             ev_pair[0].record()
-        if self.tc:
-            # criterion + backward in one pass: four warps of the backward kernel form dlogits from the logits and labels
+        if self.tc and self.fused_update:
+            # criterion + backward in one pass (four warps of the backward kernel form dlogits from the logits and
+            # labels); the split partials stay in scratch for the update kernel
+            chk(lib.b200ds_mlp_loss_backward_partials_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.logits.data_ptr(),
+                                                         self.y.data_ptr(), B, F, H, self.counter.data_ptr(),
+                                                         self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
+        elif self.tc:
             chk(lib.b200ds_mlp_loss_backward_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.params.data_ptr(),
                                                 self.logits.data_ptr(), self.y.data_ptr(), B, F, H, self.loss.data_ptr(),
                                                 self.grads.data_ptr(), self.counter.data_ptr(), self.bwd_sc.data_ptr(),
@@ -257,6 +272,25 @@ class WideStep:
         # ---- exchange + Adam, and (bf16) the next step's inputs: the next batch does not need this step's
         # gradients, so it is generated on the main stream while the exchange, Adam and the new weight pack
         # run on a side stream; both are done before the next step starts
+        if self.tc and self.fused_update:
+            # finish pass + gradient exchange (W > 1, peer memory) + Adam + operand pack: one kernel.  With several
+            # ranks it mostly waits on NVLink round trips, so it runs on a side stream beside the generator.
+            def update(stream_handle):
+                chk(lib.b200ds_update_tc(self.ctx, self.bwd_sc.data_ptr(), self.bwd_sc.numel(), B, F, H, self.params.data_ptr(),
+                                         self.grads.data_ptr(), self.m.data_ptr(), self.v.data_ptr(), self.wq.data_ptr(),
+                                         LR, 0.9, 0.999, 1e-8, 0, self.counter.data_ptr(), self.loss.data_ptr(), stream_handle))
+            if self.world == 1:
+                update(st)
+                self.gen_next(st)
+                return
+            main = torch.cuda.current_stream()
+            fork = torch.cuda.Event(); fork.record(main)
+            self.side.wait_event(fork)
+            update(self.side.cuda_stream)
+            join = torch.cuda.Event(); join.record(self.side)
+            self.gen_next(st)
+            main.wait_event(join)
+            return
         if self.tc and self.p2p:
             # the exchange kernel mostly waits on NVLink round trips (at most one CTA per SM): it overlaps with
             # the generator.  (With one rank the same fork was measured and gains nothing: the generator fills
@@ -412,7 +446,7 @@ def run_ours(a):
         e2e = bench_e2e(lib, ctx, dev, wl, world, a, barrier, precision)
         trace("e2e done")
         out.update(dict(value=value, ms_per_step=ms_per_step, roofline=roof, e2e=e2e, clocks=clk.summary(),
-                        gpu_launches=K * ws.launches_per_step, wall_s=wall, loss_last=loss_last,
+                        gpu_launches=K * ws.launches, wall_s=wall, loss_last=loss_last,
                         config={"workload": f"{a.workload}: train.py step, F={wl['F']} H={wl['H']}, {wl['B']} samples/GPU/step "
                                             f"generated on device (Philox4x32-10), Adam, {world} rank(s)",
                                 "per_gpu_batch": wl["B"], "n_features": wl["F"], "hidden": wl["H"], "parallelism": f"dp{world}",

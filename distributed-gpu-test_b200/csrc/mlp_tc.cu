@@ -25,6 +25,8 @@
 //                 dW2[n]  = sum_k w1q[n,k] S[n,k]  (= sum_b dz[b] h[b,n]),  db2 = sum_b dz[b].
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "adam.cuh"
+#include "p2p.cuh"
 #include <type_traits>
 #include "philox.cuh"
 
@@ -409,10 +411,12 @@ __global__ void __launch_bounds__(kBwdLossThreads, 1)
 mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __restrict__ w1q,
                   const float* __restrict__ dz, const float* __restrict__ ylab, float fbatch,
                   float* __restrict__ partial /* [splits][H][32] */, float* __restrict__ db2_part /* [splits] */,
-                  float* __restrict__ loss_part /* [splits] */, int n_btiles, int hidden, int nb, int n_groups, int n_splits) {
+                  float* __restrict__ loss_part /* [splits] */, unsigned long long* __restrict__ step_counter,
+                  int n_btiles, int hidden, int nb, int n_groups, int n_splits) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int group = blockIdx.x % n_groups, split = blockIdx.x / n_groups;
+  if (step_counter && blockIdx.x == 0 && threadIdx.x == 0) *step_counter += 1ull;   // nothing in this kernel reads it
   unsigned char* w1s = smem;                                           // [nb][8192]
   unsigned char* xs = w1s + (size_t)nb * kTileBytes;                   // [stages][8192]
   BwdSmem* sh = reinterpret_cast<BwdSmem*>(xs + kBwdXStages * kTileBytes);
@@ -691,6 +695,210 @@ mlp_bwd_tc_finish(const float* __restrict__ partial, const float* __restrict__ d
   }
 }
 
+// ------------------------------------------------------------------ finish + exchange + Adam + operand pack
+// Everything between the backward kernel and the next forward as ONE launch: the split partials of
+// S are summed (mlp_bwd_tc_finish), the gradients of the W ranks are exchanged through peer memory
+// and summed in rank order (p2p.cu; skipped for one rank), Adam is applied (adam.cu) and the new
+// W1 / b1 are packed to bf16 with the partials of v = w1q^T w2 (pack_w1_kernel).  Thread layout of
+// pack_w1_kernel: a block owns 64 hidden units, four threads per unit, eight k each; the thread
+// that owns slot k owns the parameter behind it (W1[n,k] for k < F, b1[n] at k = F, W2[n] at
+// k = F + 1; b2 belongs to thread 0 of block 0).  For one rank the result is bit-identical to the
+// three kernels it replaces.  Exchange buffer layout: [n][32] slots, then db2.
+template <bool kCounted>
+__global__ void __launch_bounds__(256)
+mlp_update_tc_kernel(const float* __restrict__ partial, const float* __restrict__ db2_part, const float* __restrict__ loss_part,
+                     int n_splits, double inv_batch, float* __restrict__ params, float* __restrict__ grads,
+                     float* __restrict__ m, float* __restrict__ v, Layout L, uint4* __restrict__ w1q, float* __restrict__ vpart,
+                     AdamScalars s, double lr, double beta1, double beta2, int64_t step,
+                     const unsigned long long* __restrict__ step_counter, float* __restrict__ loss_out, P2PDev d) {
+  __shared__ float prod[kPackRows][33];
+  __shared__ float sh[2];
+  __shared__ bool last;
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;     // H % 64 == 0: no partial blocks
+  const int lane = threadIdx.x & 31;
+  const int r8 = (int)(t & 7), c = (int)((t >> 3) & 3);
+  const int n = (int)(((t >> 5) << 3) + r8);
+  const int rl = n - blockIdx.x * kPackRows;
+  const bool boss = blockIdx.x == 0 && threadIdx.x == 0;
+  const int F = L.F;
+  // ---- split partials of S[n, 8c .. 8c+7], summed in split order
+  float S[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) S[j] = 0.f;
+  {
+    const float4* p = reinterpret_cast<const float4*>(partial + (size_t)n * 32 + 8 * c);
+    const size_t stride4 = (size_t)L.H * 8;
+    int sp = 0;
+    for (; sp + 9 <= n_splits; sp += 9) {                // 18 loads in flight: the pass is latency-bound (64 CTAs)
+      float4 a[9], b[9];
+#pragma unroll
+      for (int u = 0; u < 9; ++u) { a[u] = __ldcg(p + (size_t)(sp + u) * stride4); b[u] = __ldcg(p + (size_t)(sp + u) * stride4 + 1); }
+#pragma unroll
+      for (int u = 0; u < 9; ++u) {
+        S[0] += a[u].x; S[1] += a[u].y; S[2] += a[u].z; S[3] += a[u].w;
+        S[4] += b[u].x; S[5] += b[u].y; S[6] += b[u].z; S[7] += b[u].w;
+      }
+    }
+    for (; sp < n_splits; ++sp) {
+      const float4 a = __ldcg(p + (size_t)sp * stride4), b = __ldcg(p + (size_t)sp * stride4 + 1);
+      S[0] += a.x; S[1] += a.y; S[2] += a.z; S[3] += a.w;
+      S[4] += b.x; S[5] += b.y; S[6] += b.z; S[7] += b.w;
+    }
+  }
+  if (threadIdx.x == 0) {                                // the optimizer's scalars
+    double tt = kCounted ? (double)(*step_counter) : (double)step;
+    double bc1 = 1.0 - pow(beta1, tt);
+    double bc2 = 1.0 - pow(beta2, tt);
+    sh[0] = (float)(-(lr / bc1));
+    sh[1] = (float)sqrt(bc2);
+  }
+  // ---- local gradients of this thread's slots
+  float w2 = params[L.off_w2() + n];
+  float b1 = params[L.off_b1() + n];
+  const float b1hi = __bfloat162float(__float2bfloat16(b1));
+  float pw[8];                                           // the parameter behind each slot
+  float g[8], tk[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int k = 8 * c + j;
+    float wq = 0.f;
+    pw[j] = 0.f;
+    if (k < F) {
+      pw[j] = params[L.off_w1() + (int64_t)n * F + k];
+      wq = __bfloat162float(__float2bfloat16(pw[j]));
+    } else if (k == F) {
+      pw[j] = b1;
+      wq = b1hi;
+    } else if (k == F + 1) {
+      pw[j] = w2;
+      wq = __bfloat162float(__float2bfloat16(b1 - b1hi));
+    }
+    g[j] = k <= F ? w2 * S[j] : 0.f;
+    tk[j] = wq * S[j];
+  }
+  // dW2[n] = sum_k w1q[n,k] S[n,k]: the butterfly a 32-lane warp_sum over lane = k makes (k xor 16, 8 across the
+  // row's four threads, k xor 4, 2, 1 inside the thread)
+#pragma unroll
+  for (int j = 0; j < 8; ++j) tk[j] += __shfl_xor_sync(0xffffffffu, tk[j], 16);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) tk[j] += __shfl_xor_sync(0xffffffffu, tk[j], 8);
+  {
+    const float a0 = tk[0] + tk[4], a1 = tk[1] + tk[5], a2 = tk[2] + tk[6], a3 = tk[3] + tk[7];
+    const float c0 = a0 + a2, c1 = a1 + a3;
+    const float d2 = c0 + c1;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (8 * c + j == F + 1) g[j] = d2;
+  }
+  float gb2 = 0.f;
+  if (boss) for (int sp = 0; sp < n_splits; ++sp) gb2 += db2_part[sp];
+  // ---- exchange over peer memory (p2p.cu's protocol), rank-order sum
+  if (d.world > 1) {
+    const unsigned long long e = *d.epoch + 1;
+    const int64_t half = (int64_t)(e & 1) * d.cap;
+    float4* mine = reinterpret_cast<float4*>(d.xchg[d.rank] + half + (size_t)n * 32 + 8 * c);
+    mine[0] = make_float4(g[0], g[1], g[2], g[3]);
+    mine[1] = make_float4(g[4], g[5], g[6], g[7]);
+    if (boss) d.xchg[d.rank][half + (size_t)L.H * 32] = gb2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      last = atomicAdd(&d.tickets[0], 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last && threadIdx.x < d.world) {
+      __threadfence_system();
+      st_release_sys(&d.flags[threadIdx.x][d.rank], e);
+      if (threadIdx.x == 0) d.tickets[0] = 0u;
+    }
+    if (threadIdx.x < d.world) {
+      const unsigned long long* f = &d.flags[d.rank][threadIdx.x];
+      unsigned long long spins = 0;
+      while (ld_acquire_sys(f) < e) {
+        if (++spins > (1ull << 26)) __trap();
+      }
+    }
+    __syncthreads();
+    float4 lo4 = make_float4(0.f, 0.f, 0.f, 0.f), hi4 = lo4;
+    float sb2 = 0.f;
+    for (int w = 0; w < d.world; ++w) {
+      const float* base = d.xchg[w] + half;
+      const float4 a = ld_peer(reinterpret_cast<const float4*>(base + (size_t)n * 32 + 8 * c));
+      const float4 b = ld_peer(reinterpret_cast<const float4*>(base + (size_t)n * 32 + 8 * c) + 1);
+      if (w == 0) { lo4 = a; hi4 = b; }
+      else { lo4.x += a.x; lo4.y += a.y; lo4.z += a.z; lo4.w += a.w; hi4.x += b.x; hi4.y += b.y; hi4.z += b.z; hi4.w += b.w; }
+      if (boss) {
+        float vb;
+        asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(vb) : "l"(base + (size_t)L.H * 32) : "memory");
+        sb2 = w == 0 ? vb : sb2 + vb;
+      }
+    }
+    g[0] = lo4.x; g[1] = lo4.y; g[2] = lo4.z; g[3] = lo4.w; g[4] = hi4.x; g[5] = hi4.y; g[6] = hi4.z; g[7] = hi4.w;
+    gb2 = sb2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      if (atomicAdd(&d.tickets[1], 1u) == gridDim.x - 1) {
+        d.tickets[1] = 0u;
+        *d.epoch = e;
+        __threadfence();
+      }
+    }
+  } else {
+    __syncthreads();                                     // sh[] written
+  }
+  // ---- Adam on the parameters this thread owns; the summed gradient goes back to the flat bucket
+  const float neg_step_size = sh[0], bc2_sqrt = sh[1];
+  float b1_new = b1, w2_new = w2;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int k = 8 * c + j;
+    int64_t idx = -1;
+    if (k < F) idx = L.off_w1() + (int64_t)n * F + k;
+    else if (k == F) idx = L.off_b1() + n;
+    else if (k == F + 1) idx = L.off_w2() + n;
+    if (idx >= 0) {
+      float mm = m[idx], vv = v[idx];
+      grads[idx] = g[j];
+      adam_one(pw[j], g[j], mm, vv, s, neg_step_size, bc2_sqrt);
+      params[idx] = pw[j]; m[idx] = mm; v[idx] = vv;
+      if (k == F) b1_new = pw[j];
+      if (k == F + 1) w2_new = pw[j];
+    }
+  }
+  if (boss) {
+    const int64_t idx = L.off_b2();
+    float pp = params[idx], mm = m[idx], vv = v[idx];
+    grads[idx] = gb2;
+    adam_one(pp, gb2, mm, vv, s, neg_step_size, bc2_sqrt);
+    params[idx] = pp; m[idx] = mm; v[idx] = vv;
+    if (loss_part) {             // fused loss: mean over the batch, split partials summed in split order in double
+      double ls = 0.0;
+      for (int sp = 0; sp < n_splits; ++sp) ls += (double)loss_part[sp];
+      *loss_out = (float)(ls * inv_batch);
+    }
+  }
+  // ---- bf16 pack of the new W1 / b1 and the partials of v (pack_w1_kernel)
+  b1_new = __shfl_sync(0xffffffffu, b1_new, r8 + 8 * (F >> 3));
+  w2_new = __shfl_sync(0xffffffffu, w2_new, r8 + 8 * ((F + 1) >> 3));
+  (void)lane;
+  const __nv_bfloat16 hi = __float2bfloat16(b1_new);
+  const __nv_bfloat16 lo = __float2bfloat16(b1_new - __bfloat162float(hi));
+  __nv_bfloat16 q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int k = 8 * c + j;
+    q[j] = k < F ? __float2bfloat16(pw[j]) : (k == F ? hi : (k == F + 1 ? lo : __float2bfloat16(0.f)));
+    prod[rl][k] = w2_new * __bfloat162float(q[j]);
+  }
+  w1q[t] = *reinterpret_cast<uint4*>(q);
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float a = 0.f;
+    for (int r = 0; r < kPackRows; ++r) a += prod[r][threadIdx.x];
+    vpart[(size_t)blockIdx.x * 32 + threadIdx.x] = a;
+  }
+}
+
 // ------------------------------------------------------------------ host side
 struct FwdPlan { int slices, slice_rows, ctas_per_slice, n_btiles; size_t smem; };
 struct BwdPlan { int nb, groups, splits, n_btiles; size_t smem; };
@@ -843,12 +1051,13 @@ size_t b200ds_mlp_backward_tc_scratch_bytes(int64_t batch, int n_features, int h
 static int launch_backward_tc(const char* who, const void* xq_dev, const void* wq_dev, const float* params_dev,
                               const float* dz_or_logits_dev, const float* y_dev, float* loss_dev, uint64_t* step_counter_dev,
                               int64_t batch, int n_features, int hidden, float* grads_dev, void* scratch_dev,
-                              size_t scratch_bytes, uintptr_t stream) {
+                              size_t scratch_bytes, bool finish, uintptr_t stream) {
   const bool fused = y_dev != nullptr;
   B200_REQUIRE(tc_shape_ok(batch, n_features, hidden),
                "%s: needs F <= %d, H %% 128 == 0, batch %% 128 == 0 (got B=%lld F=%d H=%d)", who, KP - 2,
                (long long)batch, n_features, hidden);
-  B200_REQUIRE(xq_dev && wq_dev && params_dev && dz_or_logits_dev && grads_dev, "%s: null pointer", who);
+  B200_REQUIRE(xq_dev && wq_dev && dz_or_logits_dev, "%s: null pointer", who);
+  B200_REQUIRE(!finish || (params_dev && grads_dev), "%s: null pointer", who);
   B200_REQUIRE((((uintptr_t)dz_or_logits_dev) & 15) == 0 && (((uintptr_t)y_dev) & 15) == 0,
                "%s: logits / dlogits / labels must be 16-byte aligned", who);
   BwdPlan bp;
@@ -868,15 +1077,18 @@ static int launch_backward_tc(const char* who, const void* xq_dev, const void* w
   const unsigned char* w1q = reinterpret_cast<const unsigned char*>(wq_dev);
   float* db2_part = reinterpret_cast<float*>(scratch_dev) + (size_t)bp.splits * hidden * 32;
   float* loss_part = db2_part + bp.splits;
+  // without the finish pass the step counter is advanced by the backward kernel itself
+  unsigned long long* ctr_in_kernel = finish ? nullptr : reinterpret_cast<unsigned long long*>(step_counter_dev);
   if (fused)
     mlp_bwd_tc_kernel<true><<<bp.groups * bp.splits, kBwdLossThreads, bp.smem, st>>>(
         reinterpret_cast<const unsigned char*>(xq_dev), w1q, dz_or_logits_dev, y_dev, (float)batch,
-        reinterpret_cast<float*>(scratch_dev), db2_part, loss_part, bp.n_btiles, hidden, bp.nb, bp.groups, bp.splits);
+        reinterpret_cast<float*>(scratch_dev), db2_part, loss_part, ctr_in_kernel, bp.n_btiles, hidden, bp.nb, bp.groups, bp.splits);
   else
     mlp_bwd_tc_kernel<false><<<bp.groups * bp.splits, kBwdThreads, bp.smem, st>>>(
         reinterpret_cast<const unsigned char*>(xq_dev), w1q, dz_or_logits_dev, nullptr, (float)batch,
-        reinterpret_cast<float*>(scratch_dev), db2_part, loss_part, bp.n_btiles, hidden, bp.nb, bp.groups, bp.splits);
+        reinterpret_cast<float*>(scratch_dev), db2_part, loss_part, ctr_in_kernel, bp.n_btiles, hidden, bp.nb, bp.groups, bp.splits);
   B200_LAUNCH_CHECK();
+  if (!finish) return B200DS_OK;
   int fgrid = (hidden + 7) / 8;
   if (fgrid > sm_count() * 8) fgrid = sm_count() * 8;
   mlp_bwd_tc_finish<<<fgrid, 256, 0, st>>>(reinterpret_cast<const float*>(scratch_dev), db2_part, bp.splits, params_dev, L,
@@ -890,7 +1102,7 @@ int b200ds_mlp_backward_tc(const void* xq_dev, const void* wq_dev, const float* 
                            const float* dlogits_dev, int64_t batch, int n_features, int hidden,
                            float* grads_dev, void* scratch_dev, size_t scratch_bytes, uintptr_t stream) {
   return launch_backward_tc("mlp_backward_tc", xq_dev, wq_dev, params_dev, dlogits_dev, nullptr, nullptr, nullptr, batch,
-                            n_features, hidden, grads_dev, scratch_dev, scratch_bytes, stream);
+                            n_features, hidden, grads_dev, scratch_dev, scratch_bytes, true, stream);
 }
 
 int b200ds_mlp_loss_backward_tc(const void* xq_dev, const void* wq_dev, const float* params_dev,
@@ -899,7 +1111,58 @@ int b200ds_mlp_loss_backward_tc(const void* xq_dev, const void* wq_dev, const fl
                                 size_t scratch_bytes, uintptr_t stream) {
   B200_REQUIRE(y_dev && loss_dev, "mlp_loss_backward_tc: null pointer");
   return launch_backward_tc("mlp_loss_backward_tc", xq_dev, wq_dev, params_dev, logits_dev, y_dev, loss_dev, step_counter_dev,
-                            batch, n_features, hidden, grads_dev, scratch_dev, scratch_bytes, stream);
+                            batch, n_features, hidden, grads_dev, scratch_dev, scratch_bytes, true, stream);
+}
+
+int b200ds_mlp_loss_backward_partials_tc(const void* xq_dev, const void* wq_dev, const float* logits_dev, const float* y_dev,
+                                         int64_t batch, int n_features, int hidden, uint64_t* step_counter_dev,
+                                         void* scratch_dev, size_t scratch_bytes, uintptr_t stream) {
+  B200_REQUIRE(y_dev != nullptr, "mlp_loss_backward_partials_tc: null pointer");
+  return launch_backward_tc("mlp_loss_backward_partials_tc", xq_dev, wq_dev, nullptr, logits_dev, y_dev, nullptr, step_counter_dev,
+                            batch, n_features, hidden, nullptr, scratch_dev, scratch_bytes, false, stream);
+}
+
+int64_t b200ds_update_tc_exchange_elems(int hidden) { return (int64_t)hidden * 32 + 4; }
+
+int b200ds_update_tc(b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_bytes, int64_t batch, int n_features, int hidden,
+                     float* params_dev, float* grads_dev, float* exp_avg_dev, float* exp_avg_sq_dev, void* wq_dev,
+                     double lr, double beta1, double beta2, double eps, int64_t step, const uint64_t* step_counter_dev,
+                     float* loss_dev, uintptr_t stream) {
+  B200_REQUIRE(ctx != nullptr, "update_tc: null context");
+  B200_REQUIRE(tc_shape_ok(batch, n_features, hidden),
+               "update_tc: needs F <= %d, H %% 128 == 0, batch %% 128 == 0 (got B=%lld F=%d H=%d)", KP - 2,
+               (long long)batch, n_features, hidden);
+  B200_REQUIRE(params_dev && grads_dev && exp_avg_dev && exp_avg_sq_dev && wq_dev, "update_tc: null pointer");
+  B200_REQUIRE(step_counter_dev != nullptr || step >= 1, "update_tc: step must be >= 1 (t after the increment)");
+  BwdPlan bp;
+  bwd_plan(batch, hidden, &bp);
+  size_t need = b200ds_mlp_backward_tc_scratch_bytes(batch, n_features, hidden);
+  B200_REQUIRE(scratch_dev && scratch_bytes >= need, "update_tc: scratch too small (%zu < %zu)", scratch_bytes, need);
+  const int W = ctx->world;
+  B200_REQUIRE(W == 1 || ctx->p2p_cap >= b200ds_update_tc_exchange_elems(hidden),
+               "update_tc: %d ranks need b200ds_ctx_enable_p2p(ctx, >= %lld) first", W,
+               (long long)b200ds_update_tc_exchange_elems(hidden));
+  Layout L{n_features, hidden};
+  const float* partial = reinterpret_cast<const float*>(scratch_dev);
+  const float* db2_part = partial + (size_t)bp.splits * hidden * 32;
+  const float* loss_part = loss_dev ? db2_part + bp.splits : nullptr;
+  unsigned char* w1q = reinterpret_cast<unsigned char*>(wq_dev);
+  float* vpart = reinterpret_cast<float*>(w1q + (size_t)hidden * KP * 2);
+  const AdamScalars s = make_adam_scalars(beta1, beta2, eps, W > 1 ? (float)(1.0 / W) : 1.f);
+  const P2PDev d = make_p2p_dev(ctx);
+  const int grid = hidden / kPackRows;                   // all resident at once (<= 128 for H <= 8192): they wait on each other
+  B200_REQUIRE(W == 1 || grid <= sm_count(), "update_tc: H = %d needs more CTAs than the GPU can keep resident", hidden);
+  if (step_counter_dev)
+    mlp_update_tc_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(
+        partial, db2_part, loss_part, bp.splits, 1.0 / (double)batch, params_dev, grads_dev, exp_avg_dev, exp_avg_sq_dev, L,
+        reinterpret_cast<uint4*>(wq_dev), vpart, s, lr, beta1, beta2, 0,
+        reinterpret_cast<const unsigned long long*>(step_counter_dev), loss_dev, d);
+  else
+    mlp_update_tc_kernel<false><<<grid, 256, 0, as_stream(stream)>>>(
+        partial, db2_part, loss_part, bp.splits, 1.0 / (double)batch, params_dev, grads_dev, exp_avg_dev, exp_avg_sq_dev, L,
+        reinterpret_cast<uint4*>(wq_dev), vpart, s, lr, beta1, beta2, step, nullptr, loss_dev, d);
+  B200_LAUNCH_CHECK();
+  return B200DS_OK;
 }
 
 }  // extern "C"

@@ -18,35 +18,12 @@
 // all reads of that half -- has completed.
 #include "adam.cuh"
 #include "ctx.cuh"
+#include "p2p.cuh"
 #include <string.h>
 
 namespace b200ds {
 
 constexpr int kP2PThreads = 256;
-
-struct P2PDev {
-  int world, rank;
-  int64_t cap;                              // floats per half of an exchange buffer
-  float* xchg[B200DS_P2P_MAX_WORLD];        // every rank's exchange buffer (own entry = local memory)
-  unsigned long long* flags[B200DS_P2P_MAX_WORLD];   // every rank's flag row: flags[p][r] = last epoch rank r published to p
-  unsigned long long* epoch;                // local: epochs completed
-  unsigned int* tickets;                    // local: [0] copy-phase arrivals, [1] exit arrivals
-};
-
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-// peer data: never through this SM's L1 (the line may be a stale copy from two epochs ago)
-__device__ __forceinline__ float4 ld_peer(const float4* p) {
-  float4 v;
-  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
-  return v;
-}
 
 template <bool kCounted>
 __global__ void __launch_bounds__(kP2PThreads)
@@ -209,13 +186,7 @@ int b200ds_allreduce_adam_p2p(b200ds_ctx* ctx, float* params_dev, float* grads_d
   B200_REQUIRE(((((uintptr_t)params_dev) | ((uintptr_t)grads_dev) | ((uintptr_t)exp_avg_dev) | ((uintptr_t)exp_avg_sq_dev)) & 15) == 0,
                "allreduce_adam_p2p: buffers must be 16-byte aligned");
   B200_REQUIRE(step_counter_dev != nullptr || step >= 1, "allreduce_adam_p2p: step must be >= 1 (t after the increment)");
-  P2PDev d;
-  memset(&d, 0, sizeof(d));
-  d.world = ctx->world; d.rank = ctx->rank; d.cap = ctx->p2p_cap;
-  for (int w = 0; w < ctx->world; ++w) { d.xchg[w] = ctx->p2p_xchg[w]; d.flags[w] = ctx->p2p_flags[w]; }
-  unsigned long long* words = ctx->p2p_flags[ctx->rank];
-  d.epoch = words + B200DS_P2P_MAX_WORLD;
-  d.tickets = reinterpret_cast<unsigned int*>(words + B200DS_P2P_MAX_WORLD + 1);
+  const P2PDev d = make_p2p_dev(ctx);
   const AdamScalars s = make_adam_scalars(beta1, beta2, eps, ctx->world > 1 ? (float)(1.0 / ctx->world) : 1.f);
   // every CTA spins in phase 2, so all of them must be resident at once: at most one CTA per SM
   int64_t want = ((n >> 2) + kP2PThreads - 1) / kP2PThreads;

@@ -1,0 +1,47 @@
+// Device-side view of the peer-memory exchange set up by b200ds_ctx_enable_p2p (p2p.cu), shared by
+// the kernels that publish into it and read from it.
+#pragma once
+#include "ctx.cuh"
+#include <string.h>
+
+namespace b200ds {
+
+struct P2PDev {
+  int world, rank;
+  int64_t cap;                              // floats per half of an exchange buffer
+  float* xchg[B200DS_P2P_MAX_WORLD];        // every rank's exchange buffer (own entry = local memory)
+  unsigned long long* flags[B200DS_P2P_MAX_WORLD];   // every rank's flag row: flags[p][r] = last epoch rank r published to p
+  unsigned long long* epoch;                // local: epochs completed
+  unsigned int* tickets;                    // local: [0] copy-phase arrivals, [1] exit arrivals
+};
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// peer data: never through this SM's L1 (the line may be a stale copy from two epochs ago)
+__device__ __forceinline__ float4 ld_peer(const float4* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+// words of the local flag allocation: flag row (MAX_WORLD x u64) | epoch (u64) | tickets (2 x u32)
+inline P2PDev make_p2p_dev(const b200ds_ctx* ctx) {
+  P2PDev d;
+  memset(&d, 0, sizeof(d));
+  d.world = ctx->world; d.rank = ctx->rank; d.cap = ctx->p2p_cap;
+  for (int w = 0; w < ctx->world; ++w) { d.xchg[w] = ctx->p2p_xchg[w]; d.flags[w] = ctx->p2p_flags[w]; }
+  unsigned long long* words = ctx->p2p_flags[ctx->rank];
+  if (words) {
+    d.epoch = words + B200DS_P2P_MAX_WORLD;
+    d.tickets = reinterpret_cast<unsigned int*>(words + B200DS_P2P_MAX_WORLD + 1);
+  }
+  return d;
+}
+
+}  // namespace b200ds

@@ -263,6 +263,27 @@ B200DS_API int b200ds_allreduce_adam_p2p(b200ds_ctx* ctx, float* params_dev, flo
                                          double beta1, double beta2, double eps, int64_t step,
                                          const uint64_t* step_counter_dev, uintptr_t stream);
 
+/* ---- everything between the backward kernel and the next forward as one launch -------
+ * b200ds_mlp_loss_backward_partials_tc = b200ds_mlp_loss_backward_tc without its finish pass:
+ * the split partials stay in `scratch` (step_counter_dev is advanced by the kernel).
+ * b200ds_update_tc then does, in ONE kernel: the finish pass (gradients from the partials, loss
+ * mean into loss_dev if non-NULL), the gradient exchange over peer memory for W > 1 (protocol of
+ * b200ds_allreduce_adam_p2p; needs b200ds_ctx_enable_p2p(ctx, >= b200ds_update_tc_exchange_elems(H))),
+ * Adam (t = step, or *step_counter_dev), and the bf16 operand pack of the updated W1 / b1 into
+ * wq_dev (what b200ds_pack_params_bf16 would produce).  grads_dev receives the (summed) gradients.
+ * For one rank the result is bit-identical to b200ds_mlp_loss_backward_tc + b200ds_adam_step +
+ * b200ds_pack_params_bf16.  Every rank must make the same sequence of calls. */
+B200DS_API int b200ds_mlp_loss_backward_partials_tc(const void* xq_dev, const void* wq_dev, const float* logits_dev,
+                                                    const float* y_dev, int64_t batch, int n_features, int hidden,
+                                                    uint64_t* step_counter_dev, void* scratch_dev,
+                                                    size_t scratch_bytes, uintptr_t stream);
+B200DS_API int64_t b200ds_update_tc_exchange_elems(int hidden);
+B200DS_API int b200ds_update_tc(b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_bytes, int64_t batch,
+                                int n_features, int hidden, float* params_dev, float* grads_dev,
+                                float* exp_avg_dev, float* exp_avg_sq_dev, void* wq_dev, double lr, double beta1,
+                                double beta2, double eps, int64_t step, const uint64_t* step_counter_dev,
+                                float* loss_dev, uintptr_t stream);
+
 /* ---- end-to-end step with HOST buffers (what bench.py's `e2e` times) ---------------
  * One call = train.py:104-115 for one batch: H2D of x,y from (pinned) host memory,
  * forward, loss, backward, all-reduce, Adam (t = step0 + 1), D2H of the loss, and a

@@ -220,6 +220,56 @@ def test_fused_loss_backward_equals_loss_then_backward(lib, cuda_dev, B, F, H):
     assert int(ca) == 1 and int(cb) == 2
 
 
+@pytest.mark.parametrize("B,F,H", [(128, 20, 128), (1024, 20, 384), (65536, 20, 4096), (384, 7, 640), (256, 30, 256), (256, 1, 128)])
+def test_fused_update_equals_finish_adam_pack(lib, cuda_dev, B, F, H):
+    """b200ds_mlp_loss_backward_partials_tc + b200ds_update_tc (one rank) against
+    b200ds_mlp_loss_backward_tc + b200ds_adam_step + b200ds_pack_params_bf16 over three steps:
+    parameters, Adam moments, gradients, the packed operand and the loss bit for bit."""
+    torch.manual_seed(7 * B + H)
+    flat = ora.flatten(ora.init_params(F, H))
+    P = flat.numel(); Ppad = (P + 3) // 4 * 4
+    z = lambda n: torch.zeros(n, dtype=torch.float32, device=cuda_dev)      # noqa: E731
+    st = [dict(p=z(Ppad), g=z(Ppad), m=z(Ppad), v=z(Ppad), loss=z(1), ctr=torch.zeros(1, dtype=torch.int64, device=cuda_dev),
+               wq=torch.zeros(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=cuda_dev),
+               sc=torch.zeros(lib.b200ds_mlp_backward_tc_scratch_bytes(B, F, H), dtype=torch.uint8, device=cuda_dev)) for _ in range(2)]
+    for s_ in st:
+        s_["p"][:P] = flat.to(cuda_dev)
+        _chk(lib.b200ds_pack_params_bf16(s_["p"].data_ptr(), F, H, s_["wq"].data_ptr(), _st()))
+    ctx = C.c_void_p()
+    _chk(lib.b200ds_ctx_create(0, 0, 1, None, C.byref(ctx)))
+    xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=cuda_dev)
+    lg = z(B)
+    args = (1e-3, 0.9, 0.999, 1e-8)
+    for step in range(1, 4):
+        x = torch.randn(B, F, device=cuda_dev)
+        y = (x[:, : max(1, F // 2)].sum(dim=1) > 0).float().contiguous()
+        _chk(lib.b200ds_pack_x_bf16(x.data_ptr(), B, F, xq.data_ptr(), _st()))
+        a, b = st
+        _chk(lib.b200ds_mlp_forward_tc(xq.data_ptr(), a["wq"].data_ptr(), a["p"].data_ptr(), B, F, H, lg.data_ptr(), _st()))
+        _chk(lib.b200ds_mlp_loss_backward_tc(xq.data_ptr(), a["wq"].data_ptr(), a["p"].data_ptr(), lg.data_ptr(), y.data_ptr(), B, F, H,
+                                             a["loss"].data_ptr(), a["g"].data_ptr(), a["ctr"].data_ptr(), a["sc"].data_ptr(),
+                                             a["sc"].numel(), _st()))
+        ga = a["g"].clone()
+        _chk(lib.b200ds_adam_step(a["p"].data_ptr(), a["g"].data_ptr(), a["m"].data_ptr(), a["v"].data_ptr(), Ppad, *args, step, 1.0, 0, _st()))
+        _chk(lib.b200ds_pack_params_bf16(a["p"].data_ptr(), F, H, a["wq"].data_ptr(), _st()))
+        _chk(lib.b200ds_mlp_forward_tc(xq.data_ptr(), b["wq"].data_ptr(), b["p"].data_ptr(), B, F, H, lg.data_ptr(), _st()))
+        _chk(lib.b200ds_mlp_loss_backward_partials_tc(xq.data_ptr(), b["wq"].data_ptr(), lg.data_ptr(), y.data_ptr(), B, F, H,
+                                                      b["ctr"].data_ptr(), b["sc"].data_ptr(), b["sc"].numel(), _st()))
+        if step % 2:
+            _chk(lib.b200ds_update_tc(ctx, b["sc"].data_ptr(), b["sc"].numel(), B, F, H, b["p"].data_ptr(), b["g"].data_ptr(),
+                                      b["m"].data_ptr(), b["v"].data_ptr(), b["wq"].data_ptr(), *args, step, None,
+                                      b["loss"].data_ptr(), _st()))
+        else:
+            _chk(lib.b200ds_update_tc(ctx, b["sc"].data_ptr(), b["sc"].numel(), B, F, H, b["p"].data_ptr(), b["g"].data_ptr(),
+                                      b["m"].data_ptr(), b["v"].data_ptr(), b["wq"].data_ptr(), *args, 0, b["ctr"].data_ptr(),
+                                      b["loss"].data_ptr(), _st()))
+        torch.cuda.synchronize()
+        assert torch.equal(ga[:P], b["g"][:P]), step
+        for k in ("p", "m", "v", "wq", "loss", "ctr"):
+            assert torch.equal(a[k], b[k]), (k, step)
+    _chk(lib.b200ds_ctx_destroy(ctx))
+
+
 def _host_step_state(lib, dev, B, F, H, stage_batches):
     from b200ds import _lib
     torch.manual_seed(11)
