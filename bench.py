@@ -210,8 +210,11 @@ class WideStep:
         # W > 1: gradient exchange + Adam as one peer-memory kernel (NVLink loads of the peers' buckets,
         # fixed summation order); B200DS_BENCH_NCCL=1 selects ncclAllReduce + the Adam kernel instead
         self.p2p = world > 1 and not os.environ.get("B200DS_BENCH_NCCL")
-        # bf16: finish + exchange + Adam + pack as one kernel (B200DS_BENCH_UNFUSED=1: the separate kernels)
-        self.fused_update = self.tc and not os.environ.get("B200DS_BENCH_UNFUSED") and (world == 1 or self.p2p)
+        # B200DS_BENCH_FUSED_UPDATE=1: finish + exchange + Adam + pack as ONE kernel (b200ds_update_tc).  Not the
+        # default: measured on one box, 200 steps, three runs each, it is 2 us per step slower at one rank (102.5 vs
+        # 100.35 us: its 64 CTAs pull the 9.4 MB of split partials more slowly than the 512 CTAs of the finish
+        # kernel) and equal at two ranks.
+        self.fused_update = self.tc and bool(os.environ.get("B200DS_BENCH_FUSED_UPDATE")) and (world == 1 or self.p2p)
         if self.p2p:
             # collective; if any rank cannot map its peers (no peer access on this box) every rank takes the NCCL exchange
             import torch.distributed as dist
