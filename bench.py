@@ -260,6 +260,11 @@ class WideStep:
             chk(lib.b200ds_mlp_loss_backward_partials_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.logits.data_ptr(),
                                                          self.y.data_ptr(), B, F, H, self.counter.data_ptr(),
                                                          self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
+        elif self.tc and os.environ.get("B200DS_BENCH_SEPARATE_LOSS"):      # A/B arm: loss kernel, then backward
+            chk(lib.b200ds_bce_loss_grad(self.logits.data_ptr(), self.y.data_ptr(), B, self.loss.data_ptr(), self.dz.data_ptr(),
+                                         self.counter.data_ptr(), self.bce_sc.data_ptr(), self.bce_sc.numel(), st))
+            chk(lib.b200ds_mlp_backward_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.params.data_ptr(), self.dz.data_ptr(),
+                                           B, F, H, self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
         elif self.tc:
             chk(lib.b200ds_mlp_loss_backward_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.params.data_ptr(),
                                                 self.logits.data_ptr(), self.y.data_ptr(), B, F, H, self.loss.data_ptr(),
