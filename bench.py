@@ -442,7 +442,7 @@ def run_ours(a):
         # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture
         # (profiles/r01_ncu_full_tc_kernels_v3.txt: dram__bytes_read.sum + dram__bytes_write.sum); only known
         # for the configuration that was profiled
-        traffic = 4744448 if (a.workload == "wide4096" and precision == "bf16") else None
+        traffic = 5016576 if (a.workload == "wide4096" and precision == "bf16") else None
         roof = dict(bound="tensor", achieved=achieved, peak=pk["tf_sus"], unit="TFLOP/s", frac=achieved / pk["tf_sus"],
                     traffic=traffic, kernel=ws.dominant["name"], kernel_ms=k_ms, peak_source=f"{pk['src']} bf16 sustained",
                     step_frac=step_flops(**wl) / (ms_per_step / 1e3) / 1e12 / pk["tf_sus"],

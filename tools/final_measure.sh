@@ -9,8 +9,8 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
   --log-file gpurun_out/r01_launches_bench_wide4096.csv python bench.py --steps 3 --warmup 3 --no-tiny --no-cpu-baseline \
   > gpurun_out/ncu_bench.log 2>&1
 timeout 100 python tools/time_kernels.py > gpurun_out/time_kernels.log 2>&1
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:"mlp_fwd_tc_kernel|mlp_bwd_tc_kernel" \
-  --launch-skip 40 --launch-count 2 -o gpurun_out/tc_kernels_v3 -f python tools/time_kernels.py > gpurun_out/ncu_tc.log 2>&1
+SPIN=lbwd timeout 600 ncu --set full --clock-control none --import-source on -k regex:"mlp_fwd_tc_kernel|mlp_bwd_tc_kernel" \
+  --launch-skip 60 --launch-count 3 -o gpurun_out/tc_kernels_v3 -f python tools/time_kernels.py > gpurun_out/ncu_tc.log 2>&1
 tail -2 gpurun_out/ncu_tc.log
 python tools/launch_summary.py gpurun_out/r01_launches_bench_wide4096.csv | tail -9
 cat gpurun_out/time_kernels.log

@@ -22,18 +22,21 @@ _lib.check(lib.b200ds_pack_x_bf16(x.data_ptr(), B, F, xq.data_ptr(), st))
 _lib.check(lib.b200ds_pack_params_bf16(params.data_ptr(), F, H, wq.data_ptr(), st))
 def fwd(): _lib.check(lib.b200ds_mlp_forward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), B, F, H, z.data_ptr(), st))
 def bwd(): _lib.check(lib.b200ds_mlp_backward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), dz.data_ptr(), B, F, H, g.data_ptr(), sc.data_ptr(), sc.numel(), st))
+yl = (torch.rand(B, device=dev) > 0.5).float()
+ls = torch.zeros(1, device=dev)
+def lbwd(): _lib.check(lib.b200ds_mlp_loss_backward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), z.data_ptr(), yl.data_ptr(), B, F, H, ls.data_ptr(), g.data_ptr(), None, sc.data_ptr(), sc.numel(), st))
 yb = torch.empty(B, device=dev)
 def gen(): _lib.check(lib.b200ds_gen_batch_bf16(xq.data_ptr(), yb.data_ptr(), B, F, 1234, 0, None, st))
 # spin the clocks up
 t0 = time.time()
 while time.time() - t0 < 1.0:
-    fwd(); bwd()
+    fwd(); (lbwd if os.environ.get("SPIN") == "lbwd" else bwd)()
 torch.cuda.synchronize()
-for name, fn in (("gen_batch", gen), ("fwd", fwd), ("bwd+finish", bwd)):
+for name, fn in (("gen_batch", gen), ("fwd", fwd), ("bwd+finish", bwd), ("loss+bwd+finish", lbwd)):
     for _ in range(5): fn()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n = 50
     e0.record()
     for _ in range(n): fn()
     e1.record(); torch.cuda.synchronize()
-    print(f"{os.environ.get('B200DS_LIB','default'):28s} B={B} H={H} {name:14s} {1e3 * e0.elapsed_time(e1) / n:8.2f} us", flush=True)
+    print(f"{os.environ.get('B200DS_LIB','default'):28s} B={B} H={H} {name:16s} {1e3 * e0.elapsed_time(e1) / n:8.2f} us", flush=True)
