@@ -802,7 +802,7 @@ mlp_update_tc_kernel(const float* __restrict__ partial, const float* __restrict_
     if (boss) d.xchg[d.rank][half + (size_t)L.H * 32] = gb2;
     __syncthreads();
     if (threadIdx.x == 0) {
-      __threadfence_system();
+      __threadfence();                                   // device scope; the last CTA's system fence is cumulative
       last = atomicAdd(&d.tickets[0], 1u) == gridDim.x - 1;
     }
     __syncthreads();

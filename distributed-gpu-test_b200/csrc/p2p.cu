@@ -52,7 +52,7 @@ p2p_allreduce_adam_kernel(float* __restrict__ p, float* __restrict__ g, float* _
   }
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence_system();
+    __threadfence();                                     // device scope here; the last CTA's system fence below is cumulative
     last = atomicAdd(&d.tickets[0], 1u) == gridDim.x - 1;
   }
   __syncthreads();
