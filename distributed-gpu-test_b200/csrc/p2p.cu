@@ -43,13 +43,6 @@ p2p_allreduce_adam_kernel(float* __restrict__ p, float* __restrict__ g, float* _
     const float4* src = reinterpret_cast<const float4*>(g);
     for (int64_t i = t0; i < nvec; i += stride) dst[i] = src[i];
   }
-  if (threadIdx.x == 0) {                                // the optimizer's scalars while the copies drain
-    double t = kCounted ? (double)(*step_counter) : (double)step;
-    double bc1 = 1.0 - pow(beta1, t);
-    double bc2 = 1.0 - pow(beta2, t);
-    sh[0] = (float)(-(lr / bc1));
-    sh[1] = (float)sqrt(bc2);
-  }
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();                                     // device scope here; the last CTA's system fence below is cumulative
@@ -60,6 +53,13 @@ p2p_allreduce_adam_kernel(float* __restrict__ p, float* __restrict__ g, float* _
     __threadfence_system();
     st_release_sys(&d.flags[threadIdx.x][d.rank], e);
     if (threadIdx.x == 0) d.tickets[0] = 0u;
+  }
+  if (threadIdx.x == 32) {                               // the optimizer's scalars, after the publication: two double-precision
+    double t = kCounted ? (double)(*step_counter) : (double)step;      // pow() hide behind the NVLink round trip instead of delaying it
+    double bc1 = 1.0 - pow(beta1, t);
+    double bc2 = 1.0 - pow(beta2, t);
+    sh[0] = (float)(-(lr / bc1));
+    sh[1] = (float)sqrt(bc2);
   }
   // ---- 2. wait for every rank's publication (bounded: a protocol bug traps instead of hanging the box)
   if (threadIdx.x < d.world) {
