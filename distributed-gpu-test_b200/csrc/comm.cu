@@ -121,6 +121,11 @@ int b200ds_ctx_destroy(b200ds_ctx* c) {
   if (!c) return B200DS_OK;
   cudaSetDevice(c->device);
   if (c->side) cudaStreamSynchronize(c->side);
+  for (auto& g : c->sgraph)          // before the communicator: NCCL keeps it alive while a graph refers to it
+    if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
+  if (c->cap) cudaStreamDestroy(c->cap);
+  if (c->step_word) cudaFree(c->step_word);
+  if (c->step_pinned) cudaFreeHost(c->step_pinned);
   if (c->copy) { cudaStreamSynchronize(c->copy); cudaStreamDestroy(c->copy); }
   if (c->p2p_own) {
     cudaDeviceSynchronize();

@@ -20,6 +20,16 @@ struct b200ds_ctx {
   const float* pf_x = nullptr;
   const float* pf_y = nullptr;
   int pf_slot = 0;
+  // the device part of that step as a CUDA graph per staging half (captured on `cap`, replayed on the
+  // caller's stream); the Adam step number travels through step_word
+  struct StepGraph {
+    unsigned char key[192];
+    size_t key_len = 0;
+    cudaGraphExec_t exec = nullptr;
+  } sgraph[2];
+  cudaStream_t cap = nullptr;
+  unsigned long long* step_word = nullptr;     // device
+  unsigned long long* step_pinned = nullptr;   // pinned host
   // peer-memory exchange (b200ds_ctx_enable_p2p): every rank's exchange buffer and flag row,
   // own entries cudaMalloc'ed here, the others opened from the peers' IPC handles
   float* p2p_xchg[B200DS_P2P_MAX_WORLD] = {};

@@ -2,6 +2,7 @@
 // behind one C call (H2D copies, forward, loss, backward, all-reduce, Adam, loss D2H,
 // sync).  This is the call bench.py times for its `e2e` figure.
 #include "ctx.cuh"
+#include <string.h>
 
 using namespace b200ds;
 
@@ -20,7 +21,8 @@ size_t b200ds_train_step_scratch_bytes(int64_t batch, int n_features, int hidden
 // the device part of the step on staged inputs (x_dev, y_dev), loss left in b->loss
 static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const float* x_dev, const float* y_dev,
                            int64_t batch, int n_features, int hidden, double lr, double beta1, double beta2,
-                           double eps, int64_t step0, uintptr_t stream) {
+                           double eps, int64_t step0, const uint64_t* step_counter /* device word holding step0 + 1, or NULL */,
+                           uintptr_t stream) {
   const Layout L{n_features, hidden};
   const int64_t P = L.count();
   const int64_t Ppad = (P + 3) / 4 * 4;
@@ -62,10 +64,55 @@ static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const flo
   }
   if (ctx->world > 1 && ctx->p2p_cap >= Ppad)      // peer-memory exchange enabled on this context: one kernel for both
     return b200ds_allreduce_adam_p2p(ctx, b->params, b->grads, b->exp_avg, b->exp_avg_sq, Ppad, lr, beta1, beta2, eps,
-                                     step0 + 1, nullptr, stream);
+                                     step0 + 1, step_counter, stream);
   if ((rc = b200ds_allreduce_bucket(ctx, b->grads, P, stream))) return rc;
+  if (step_counter)
+    return b200ds_adam_step_counted(b->params, b->grads, b->exp_avg, b->exp_avg_sq, Ppad, lr, beta1, beta2, eps,
+                                    step_counter, scale, 0, stream);
   return b200ds_adam_step(b->params, b->grads, b->exp_avg, b->exp_avg_sq, Ppad, lr, beta1, beta2, eps,
                           step0 + 1, scale, 0, stream);
+}
+
+// The same device work as a CUDA graph: captured once per (buffers, staging half, shape, hyper-parameters) on
+// the context's capture stream, replayed on the caller's stream.  The eager call costs ~8 kernel launches of
+// host time per step; the replay one.  The Adam step number is the only thing that changes between replays:
+// it is copied into a device word before each launch.
+static int run_staged_step_graph(b200ds_ctx* ctx, const b200ds_step_bufs* b, int slot, const float* x_dev, const float* y_dev,
+                                 int64_t batch, int n_features, int hidden, double lr, double beta1, double beta2,
+                                 double eps, int64_t step0, cudaStream_t s) {
+  if (!ctx->cap) {
+    B200_CUDA(cudaStreamCreateWithFlags(&ctx->cap, cudaStreamNonBlocking));
+    B200_CUDA(cudaMalloc(&ctx->step_word, sizeof(unsigned long long)));
+    B200_CUDA(cudaHostAlloc(&ctx->step_pinned, sizeof(unsigned long long), cudaHostAllocDefault));
+  }
+  unsigned char key[192];
+  size_t n = 0;
+  memset(key, 0, sizeof(key));
+  auto put = [&](const void* p, size_t len) { memcpy(key + n, p, len); n += len; };
+  static_assert(sizeof(b200ds_step_bufs) + 2 * sizeof(void*) + sizeof(int64_t) + 2 * sizeof(int) + 4 * sizeof(double) <= sizeof(key), "key");
+  put(b, sizeof(*b)); put(&x_dev, sizeof(x_dev)); put(&y_dev, sizeof(y_dev)); put(&batch, sizeof(batch));
+  put(&n_features, sizeof(int)); put(&hidden, sizeof(int)); put(&lr, sizeof(double)); put(&beta1, sizeof(double));
+  put(&beta2, sizeof(double)); put(&eps, sizeof(double));
+  b200ds_ctx::StepGraph& g = ctx->sgraph[slot & 1];
+  if (!g.exec || g.key_len != n || memcmp(g.key, key, n) != 0) {
+    if (g.exec) { B200_CUDA(cudaGraphExecDestroy(g.exec)); g.exec = nullptr; }
+    cudaGraph_t graph = nullptr;
+    B200_CUDA(cudaStreamBeginCapture(ctx->cap, cudaStreamCaptureModeThreadLocal));
+    int rc = run_staged_step(ctx, b, x_dev, y_dev, batch, n_features, hidden, lr, beta1, beta2, eps, step0, reinterpret_cast<const uint64_t*>(ctx->step_word),
+                             (uintptr_t)ctx->cap);
+    cudaError_t e = cudaStreamEndCapture(ctx->cap, &graph);
+    if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+    B200_CUDA(e);
+    e = cudaGraphInstantiate(&g.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    B200_CUDA(e);
+    memcpy(g.key, key, n);
+    g.key_len = n;
+  }
+  *ctx->step_pinned = (unsigned long long)(step0 + 1);
+  B200_CUDA(cudaMemcpyAsync(ctx->step_word, ctx->step_pinned, sizeof(unsigned long long), cudaMemcpyHostToDevice, s));
+  B200_CUDA(cudaGraphLaunch(g.exec, s));
+  return B200DS_OK;
 }
 
 int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* b,
@@ -81,7 +128,7 @@ int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* b,
   ctx->pf_x = ctx->pf_y = nullptr;          // this call overwrites the first half of the staging buffers
   B200_CUDA(cudaMemcpyAsync(b->x_stage, x_host, sizeof(float) * batch * n_features, cudaMemcpyHostToDevice, s));
   B200_CUDA(cudaMemcpyAsync(b->y_stage, y_host, sizeof(float) * batch, cudaMemcpyHostToDevice, s));
-  int rc = run_staged_step(ctx, b, b->x_stage, b->y_stage, batch, n_features, hidden, lr, beta1, beta2, eps, step0, stream);
+  int rc = run_staged_step(ctx, b, b->x_stage, b->y_stage, batch, n_features, hidden, lr, beta1, beta2, eps, step0, nullptr, stream);
   if (rc) return rc;
   B200_CUDA(cudaMemcpyAsync(loss_host, b->loss, sizeof(float), cudaMemcpyDeviceToHost, s));
   B200_CUDA(cudaStreamSynchronize(s));
@@ -125,7 +172,10 @@ int b200ds_train_step_host_prefetch(b200ds_ctx* ctx, const b200ds_step_bufs* b,
     B200_CUDA(cudaEventRecord(ctx->ev_copied, ctx->copy));
     ctx->pf_x = x_next_host; ctx->pf_y = y_next_host; ctx->pf_slot = slot ^ 1;
   }
-  int rc = run_staged_step(ctx, b, xs, ys, batch, n_features, hidden, lr, beta1, beta2, eps, step0, stream);
+  // the staged kernels as one graph replay (the one-launch tiny class stays eager)
+  int rc = tiny_class(batch, n_features, hidden)
+               ? run_staged_step(ctx, b, xs, ys, batch, n_features, hidden, lr, beta1, beta2, eps, step0, nullptr, stream)
+               : run_staged_step_graph(ctx, b, slot, xs, ys, batch, n_features, hidden, lr, beta1, beta2, eps, step0, s);
   if (rc) return rc;
   B200_CUDA(cudaMemcpyAsync(loss_host, b->loss, sizeof(float), cudaMemcpyDeviceToHost, s));
   B200_CUDA(cudaStreamSynchronize(s));

@@ -317,7 +317,10 @@ B200DS_API int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* b
  * uses the staged copy and copies nothing; any other pointers are copied as in
  * b200ds_train_step_host.  A prefetched host buffer must stay unchanged until the call that
  * consumes it returns.  NULL next pointers = no prefetch.  Result per call: identical to
- * b200ds_train_step_host on the same batch. */
+ * b200ds_train_step_host on the same batch.  The device part of the step is captured once per
+ * (buffers, staging half, shape, hyper-parameters) as a CUDA graph on a stream of the context and
+ * replayed on the caller's stream (one launch per step instead of ~8); the graphs are destroyed
+ * by b200ds_ctx_destroy. */
 B200DS_API int b200ds_train_step_host_prefetch(b200ds_ctx* ctx, const b200ds_step_bufs* bufs,
                            const float* x_host, const float* y_host,
                            const float* x_next_host, const float* y_next_host, int64_t batch,
