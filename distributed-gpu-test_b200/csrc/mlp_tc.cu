@@ -217,26 +217,29 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
     for (int c = 0; c < NC; ++c) tma_load_1d(w1s + (size_t)c * kTileBytes, wsrc + (size_t)c * kTileBytes, kTileBytes, &sh->w_bar);
   }
   if (warp == 9) tmem_alloc<512>(&sh->tmem_slot);
-  for (int i = threadIdx.x; i < slice_rows; i += blockDim.x) w2s[i] = w2[slice * slice_rows + i];
-  {      // v = sum over the 64-row blocks of this slice: 8 warps take 1/8 of the blocks each, then a fixed-order sum
-    const int nblk = slice_rows / kPackRows;
-    if (warp < 8) {
+  tc_fence_before();
+  __syncthreads();                         // barriers and TMEM are up: the producer and the MMA issuers start at once
+  tc_fence_after();
+  if (warp < kFwdEpiWarps) {
+    // only the epilogue warps need w2 and v: they fetch them among themselves (named barrier 1, the one
+    // their tile ends use) while the first MMAs already run
+    for (int i = threadIdx.x; i < slice_rows; i += 32 * kFwdEpiWarps) w2s[i] = w2[slice * slice_rows + i];
+    {    // v = sum over the 64-row blocks of this slice: 8 warps take 1/8 of the blocks each, then a fixed-order sum
+      const int nblk = slice_rows / kPackRows;
       const float* vp = vlin + (size_t)slice * nblk * 32 + lane;
       float a = 0.f;
       for (int i = warp; i < nblk; i += 8) a += vp[(size_t)i * 32];
       sh->red[0][0][warp * 32 + lane] = a;      // red[] is free until the first tile ends
     }
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  if (threadIdx.x < 32) {
-    float a = 0.f;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (threadIdx.x < 32) {
+      float a = 0.f;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) a += (&sh->red[0][0][0])[w * 32 + threadIdx.x];
-    sh->v[threadIdx.x] = a;
+      for (int w = 0; w < 8; ++w) a += (&sh->red[0][0][0])[w * 32 + threadIdx.x];
+      sh->v[threadIdx.x] = a;
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
   }
-  __syncthreads();
   if (sh->tmem_slot != 0) __trap();        // all 512 columns are ours: the allocation can only start at 0,
   constexpr uint32_t tmem = 0;             // and a literal keeps the MMA issue path free of vector -> uniform moves
 
