@@ -72,8 +72,8 @@ pack_x_kernel(const float* __restrict__ x, int64_t batch, int F, uint4* __restri
 // shared memory, and each thread then writes one 16-byte chunk of xq (same thread->address
 // map as pack_x_kernel); thread 0 of the row evaluates the label rule (train.py:22-23) on the
 // fp32 values in the order label_rule_kernel uses.  fp32 x is never written to global memory.
-template <typename idx_t>      // uint32_t when batch*F < 2^31 (64-bit div/mod would dominate the kernel)
-__global__ void __launch_bounds__(256)
+template <typename idx_t, int PER>      // idx_t: uint32_t when batch*F < 2^31 (64-bit div/mod would dominate the kernel);
+__global__ void __launch_bounds__(256)  // PER = ceil(F/4) values per thread, a compile-time count so that the PER
 gen_batch_kernel(uint4* __restrict__ xq, float* __restrict__ y, int64_t batch, int F, uint2 key, uint64_t ctr0,
                  int64_t nthreads, uint32_t inv_nthreads /* floor(2^32 / nthreads) */, int calls,
                  const unsigned long long* __restrict__ draw_counter) {
@@ -84,27 +84,34 @@ gen_batch_kernel(uint4* __restrict__ xq, float* __restrict__ y, int64_t batch, i
   const int64_t row = ((t >> 5) << 3) + r8;
   if (row >= batch) return;                                              // whole warps (batch % 8 == 0)
   float* xr = xs[(threadIdx.x >> 5) * 8 + r8];
-  const int per = (F + 3) >> 2;                                          // values drawn by each of the 4 threads
+  // independent Philox chains of a thread are unrolled side by side (one chain alone is latency-bound)
+  constexpr int per = PER;
+  float val[PER];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int k = c * per + j;
-    if (j < per && k < F) {
-      const idx_t li = (idx_t)row * (idx_t)F + (idx_t)k;
-      idx_t tt, sub;
-      if (sizeof(idx_t) == 4) {                                          // li / nthreads by multiply-high and one correction
-        uint32_t qd = __umulhi((uint32_t)li, inv_nthreads);
-        uint32_t rm = (uint32_t)li - qd * (uint32_t)nthreads;
-        if (rm >= (uint32_t)nthreads) { ++qd; rm -= (uint32_t)nthreads; }
-        tt = (idx_t)qd; sub = (idx_t)rm;
-      } else {
-        tt = li / (idx_t)nthreads;
-        sub = li - tt * (idx_t)nthreads;
-      }
-      const uint64_t ctr = ctr0 + (uint64_t)(tt >> 2);
-      const uint4 r = philox4x32_10(make_uint4((unsigned)ctr, (unsigned)(ctr >> 32), (unsigned)sub, (unsigned)((uint64_t)sub >> 32)), key);
-      const float2 p = (tt & 2) ? box_muller(r.z, r.w) : box_muller(r.x, r.y);
-      xr[k] = normal_transform((tt & 1) ? p.y : p.x);
+  for (int j = 0; j < PER; ++j) {                                        // branch-free: a slot past F redraws column F-1 and is dropped
+    const int k = min(c * per + j, F - 1);
+    const idx_t li = (idx_t)row * (idx_t)F + (idx_t)k;
+    idx_t tt, sub;
+    if (sizeof(idx_t) == 4) {                                            // li / nthreads by multiply-high and one correction
+      uint32_t qd = __umulhi((uint32_t)li, inv_nthreads);
+      uint32_t rm = (uint32_t)li - qd * (uint32_t)nthreads;
+      const bool fix = rm >= (uint32_t)nthreads;
+      qd += fix ? 1u : 0u;
+      rm -= fix ? (uint32_t)nthreads : 0u;
+      tt = (idx_t)qd; sub = (idx_t)rm;
+    } else {
+      tt = li / (idx_t)nthreads;
+      sub = li - tt * (idx_t)nthreads;
     }
+    const uint64_t ctr = ctr0 + (uint64_t)(tt >> 2);
+    const uint4 r = philox4x32_10(make_uint4((unsigned)ctr, (unsigned)(ctr >> 32), (unsigned)sub, (unsigned)((uint64_t)sub >> 32)), key);
+    const float2 p = box_muller((tt & 2) ? r.z : r.x, (tt & 2) ? r.w : r.y);
+    val[j] = normal_transform((tt & 1) ? p.y : p.x);
+  }
+#pragma unroll
+  for (int j = 0; j < PER; ++j) {
+    const int k = c * per + j;
+    if (k < F) xr[k] = val[j];
   }
   __syncwarp();                                                          // the 4 threads of a row share a warp
   __nv_bfloat16 q[8];
@@ -976,15 +983,24 @@ static int launch_gen_batch(void* xq_dev, float* y_dev, int64_t batch, int n_fea
   int64_t threads = batch * (KP / 8);
   const unsigned blocks = (unsigned)((threads + 255) / 256);
   const uint2 key = make_uint2((unsigned)seed, (unsigned)(seed >> 32));
-  if (batch * n_features < (int64_t)1 << 31)
-    gen_batch_kernel<uint32_t><<<blocks, 256, 0, as_stream(stream)>>>(
-        reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256,
-        (uint32_t)(((uint64_t)1 << 32) / ((uint64_t)grid * 256)), calls,
-        reinterpret_cast<const unsigned long long*>(draw_counter_dev));
-  else
-    gen_batch_kernel<uint64_t><<<blocks, 256, 0, as_stream(stream)>>>(
-        reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256, 0u, calls,
-        reinterpret_cast<const unsigned long long*>(draw_counter_dev));
+  const bool small = batch * n_features < (int64_t)1 << 31;
+  const uint32_t inv = small ? (uint32_t)(((uint64_t)1 << 32) / ((uint64_t)grid * 256)) : 0u;
+#define B200_GEN_CASE(P)                                                                                                   \
+  case P:                                                                                                                  \
+    if (small)                                                                                                             \
+      gen_batch_kernel<uint32_t, P><<<blocks, 256, 0, as_stream(stream)>>>(                                                \
+          reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256, inv, calls,    \
+          reinterpret_cast<const unsigned long long*>(draw_counter_dev));                                                  \
+    else                                                                                                                   \
+      gen_batch_kernel<uint64_t, P><<<blocks, 256, 0, as_stream(stream)>>>(                                                \
+          reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256, inv, calls,    \
+          reinterpret_cast<const unsigned long long*>(draw_counter_dev));                                                  \
+    break;
+  switch ((n_features + 3) >> 2) {
+    B200_GEN_CASE(1) B200_GEN_CASE(2) B200_GEN_CASE(3) B200_GEN_CASE(4)
+    B200_GEN_CASE(5) B200_GEN_CASE(6) B200_GEN_CASE(7) B200_GEN_CASE(8)
+  }
+#undef B200_GEN_CASE
   B200_LAUNCH_CHECK();
   if (offset_advance) *offset_advance = (uint64_t)calls * 4;
   return B200DS_OK;
