@@ -204,6 +204,7 @@ class WideStep:
             self.xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=dev)
             self.wq = torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=dev)
             self.bwd_sc = torch.zeros(max(256, lib.b200ds_mlp_backward_tc_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
+            self.fwd_sc = torch.zeros(max(256, lib.b200ds_mlp_forward_tc_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
             self.dominant = dict(name="mlp_bwd_tc_kernel<LOSS> (+finish)", bound="tensor")
         # bf16: gen_batch, pack_w1, forward, loss+backward, finish, adam; fp32: philox, label, forward, loss, backward, finish, adam
         self.launches_per_step = 6 if precision == "bf16" else 7          # 4 with the fused update (set below)
@@ -247,7 +248,7 @@ class WideStep:
                 self.pack(st)
                 self.primed = True
             chk(lib.b200ds_mlp_forward_tc(self.xq.data_ptr(), self.wq.data_ptr(), self.params.data_ptr(), B, F, H,
-                                          self.logits.data_ptr(), st))
+                                          self.logits.data_ptr(), self.fwd_sc.data_ptr(), self.fwd_sc.numel(), st))
         else:
             chk(lib.b200ds_philox_normal_counted(self.x.data_ptr(), B * F, self.seed, 0, self.counter.data_ptr(), st))
             chk(lib.b200ds_label_rule(self.x.data_ptr(), self.y.data_ptr(), B, F, st))

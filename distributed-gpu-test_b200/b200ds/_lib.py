@@ -71,7 +71,9 @@ PROTOTYPES = {
     "b200ds_gen_batch_bf16": (C.c_int, [c_ptr, c_ptr, c_i64, C.c_int, c_u64, c_u64, C.POINTER(c_u64), c_stream]),
     "b200ds_gen_batch_bf16_counted": (C.c_int, [c_ptr, c_ptr, c_i64, C.c_int, c_u64, c_u64, c_ptr, c_stream]),
     "b200ds_pack_params_bf16": (C.c_int, [c_ptr, C.c_int, C.c_int, c_ptr, c_stream]),
-    "b200ds_mlp_forward_tc": (C.c_int, [c_ptr, c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_stream]),
+    "b200ds_pack_x_bf16_rows": (C.c_int, [c_ptr, c_i64, c_i64, C.c_int, c_ptr, c_stream]),
+    "b200ds_mlp_forward_tc_scratch_bytes": (C.c_size_t, [c_i64, C.c_int, C.c_int]),
+    "b200ds_mlp_forward_tc": (C.c_int, [c_ptr, c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_ptr, C.c_size_t, c_stream]),
     "b200ds_mlp_backward_tc_scratch_bytes": (C.c_size_t, [c_i64, C.c_int, C.c_int]),
     "b200ds_mlp_backward_tc": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_ptr, C.c_size_t, c_stream]),
     "b200ds_train_step_scratch_bytes": (C.c_size_t, [c_i64, C.c_int, C.c_int]),

@@ -65,7 +65,18 @@ class B200Engine:
         self.module = model
         self.training = True
         l1, l2 = _find_mlp(model)
-        self.F, self.H = l1.in_features, l1.out_features
+        self.F, self.H_model = l1.in_features, l1.out_features
+        # bf16 (BASELINE configs 3/4): the tcgen05 kernels take hidden sizes and batches in multiples of 128.
+        # A smaller model (the reference's H = 64) is carried in a flat buffer padded with hidden units whose
+        # W1 row, b1 and W2 are zero: they add nothing to the logits, receive zero gradients and stay zero
+        # under Adam, so the padded model IS the model.  Batches are padded with rows whose dlogits are zero.
+        self.H = self.H_model
+        if self.cfg["precision"] == "bf16":
+            self.H = (self.H_model + 127) // 128 * 128
+            if not self.lib.b200ds_tc_supported(128, self.F, self.H):
+                raise NotImplementedError(
+                    "bf16.enabled: the tensor-core path takes n_features <= 30 (got F=%d, H=%d); there is no silent "
+                    "fp32 substitute -- drop bf16.enabled for this model" % (self.F, self.H_model))
         self.P = self.F * self.H + 2 * self.H + 1
         self.stage = self.cfg["stage"]
         quantum = 4 * self.le.world_size if self.stage == 1 else 4      # stage 1 shards the flat vector W ways
@@ -97,24 +108,26 @@ class B200Engine:
         n_state = self.Ppad // self.le.world_size if self.stage == 1 else self.Ppad
         self.exp_avg = torch.zeros(n_state, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(n_state, dtype=torch.float32, device=dev)
-        o = 0
         self._views = []
-        for p in (l1.weight, l1.bias, l2.weight, l2.bias):
-            n = p.numel()
+        H, Hm, F = self.H, self.H_model, self.F
+        for p, o in ((l1.weight, 0), (l1.bias, H * F), (l2.weight, H * F + H), (l2.bias, H * F + 2 * H)):
+            n = p.numel()                        # offsets of the (possibly padded) layout, lengths of the model's tensors
             self.flat[o:o + n].copy_(p.detach().reshape(-1).to(torch.float32))
             p.data = self.flat[o:o + n].view(p.shape)
             p.grad = None
             self._views.append((p, o, n))
-            o += n
-        assert o == self.P
+        assert self._views[-1][1] + 1 == self.P and Hm <= H
         stream = _lib.current_stream()
         _lib.check(self.lib.b200ds_broadcast_params(self.ctx, self.flat.data_ptr(), self.P, stream), "broadcast_params")
+        self._step_tensors = []
         for p, off, n in (self._views if self.stage == 0 else []):     # keep optimizer.state_dict() meaningful
             optimizer.state[p] = {"step": torch.tensor(0.0), "exp_avg": self.exp_avg[off:off + n].view(p.shape),
                                   "exp_avg_sq": self.exp_avg_sq[off:off + n].view(p.shape)}
+            self._step_tensors.append(optimizer.state[p]["step"])
         self._x = None
         self._logits = None
         self._scratch = None
+        self._fwd_scratch = None
         self._tc = False
         self._xq = None
         self._wq = None
@@ -156,22 +169,32 @@ class B200Engine:
                              % (self.F, self.device, x.dtype, tuple(x.shape), x.device))
         x = x.contiguous()
         B = x.shape[0]
-        logits = torch.empty((B, 1), dtype=torch.float32, device=self.device)
         stream = _lib.current_stream()
-        self._tc = self.cfg["precision"] == "bf16" and bool(self.lib.b200ds_tc_supported(B, self.F, self.H))
+        self._tc = self.cfg["precision"] == "bf16"
         if self._tc:
-            # bf16 extension (BASELINE config 3/4): tcgen05 kernels on packed bf16 operands
-            self._xq = torch.empty(self.lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=self.device)
+            # bf16 extension (BASELINE config 3/4): tcgen05 kernels on packed bf16 operands; the batch is padded to
+            # a multiple of 128 rows inside the pack (zero rows, whose dlogits backward() keeps at zero)
+            Bp = (B + 127) // 128 * 128
+            self._Bp = Bp
+            logits_p = torch.empty(Bp, dtype=torch.float32, device=self.device)
+            logits = logits_p[:B].view(B, 1)
+            self._xq = torch.empty(self.lib.b200ds_tc_xq_bytes(Bp), dtype=torch.uint8, device=self.device)
             if self._wq is None:
                 self._wq = torch.empty(self.lib.b200ds_tc_wq_bytes(self.H), dtype=torch.uint8, device=self.device)
-            _lib.check(self.lib.b200ds_pack_x_bf16(x.data_ptr(), B, self.F, self._xq.data_ptr(), stream), "pack_x_bf16")
+            _lib.check(self.lib.b200ds_pack_x_bf16_rows(x.data_ptr(), B, Bp, self.F, self._xq.data_ptr(), stream), "pack_x_bf16_rows")
             if self._wq_step != self.global_steps:
                 _lib.check(self.lib.b200ds_pack_params_bf16(self.flat.data_ptr(), self.F, self.H, self._wq.data_ptr(), stream),
                            "pack_params_bf16")
                 self._wq_step = self.global_steps
-            _lib.check(self.lib.b200ds_mlp_forward_tc(self._xq.data_ptr(), self._wq.data_ptr(), self.flat.data_ptr(), B,
-                                                      self.F, self.H, logits.data_ptr(), stream), "mlp_forward_tc")
+            need = self.lib.b200ds_mlp_forward_tc_scratch_bytes(Bp, self.F, self.H)
+            if self._fwd_scratch is None or self._fwd_scratch.numel() < need:     # zeroed once; the kernel leaves it zeroed
+                self._fwd_scratch = torch.zeros(max(need, 256), dtype=torch.uint8, device=self.device)
+            fsc = self._fwd_scratch
+            _lib.check(self.lib.b200ds_mlp_forward_tc(self._xq.data_ptr(), self._wq.data_ptr(), self.flat.data_ptr(), Bp,
+                                                      self.F, self.H, logits_p.data_ptr(), fsc.data_ptr(), fsc.numel(), stream),
+                       "mlp_forward_tc")
         else:
+            logits = torch.empty((B, 1), dtype=torch.float32, device=self.device)
             _lib.check(self.lib.b200ds_mlp_forward_f32(self.flat.data_ptr(), x.data_ptr(), B, self.F, self.H,
                                                        logits.data_ptr(), stream), "mlp_forward_f32")
         self._x = x
@@ -194,9 +217,14 @@ class B200Engine:
         B = self._x.shape[0]
         stream = _lib.current_stream()
         if self._tc:
-            scratch = self._scratch_for(self.lib.b200ds_mlp_backward_tc_scratch_bytes(B, self.F, self.H))
+            Bp = self._Bp
+            if Bp != B:                       # padded rows carry dlogits = 0: they add nothing to any gradient
+                dzp = torch.zeros(Bp, dtype=torch.float32, device=self.device)
+                dzp[:B].copy_(dlogits.reshape(-1))
+                dlogits = dzp
+            scratch = self._scratch_for(self.lib.b200ds_mlp_backward_tc_scratch_bytes(Bp, self.F, self.H))
             _lib.check(self.lib.b200ds_mlp_backward_tc(self._xq.data_ptr(), self._wq.data_ptr(), self.flat.data_ptr(),
-                                                       dlogits.data_ptr(), B, self.F, self.H, self.grads.data_ptr(),
+                                                       dlogits.data_ptr(), Bp, self.F, self.H, self.grads.data_ptr(),
                                                        scratch.data_ptr(), scratch.numel(), stream), "mlp_backward_tc")
         else:
             scratch = self._scratch_for(self.lib.b200ds_mlp_backward_f32_scratch_bytes(B, self.F, self.H))
@@ -211,6 +239,8 @@ class B200Engine:
     def step(self):
         lr, b1, b2, eps = self._hyper()
         self.global_steps += 1
+        for t in self._step_tensors:          # what optimizer.state_dict() reports as Adam's t
+            t.fill_(float(self.global_steps))
         if self.stage == 1:
             # reduce-scatter -> Adam on this rank's slice -> all-gather of the parameters
             _lib.check(self.lib.b200ds_zero1_step(self.ctx, self.flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),
@@ -228,7 +258,7 @@ class B200Engine:
 
     # ------------------------------------------------------------------ fused fast paths (additions)
     def supports_fused_steps(self, batch: int) -> bool:
-        return self.F <= 32 and self.H <= 256 and 1 <= batch <= 32
+        return self.cfg["precision"] == "fp32" and self.F <= 32 and self.H <= 256 and 1 <= batch <= 32
 
     def fused_steps(self, x_all: torch.Tensor, y_all: torch.Tensor, order: torch.Tensor, first: int,
                     batch: int, n_steps: int, losses: torch.Tensor | None = None) -> torch.Tensor:
@@ -307,33 +337,91 @@ class B200Engine:
         return host_step
 
     # ------------------------------------------------------------------ train.py:125
+    _MODEL_FILE = "mp_rank_00_model_states.pt"
+
+    def _optim_file(self, rank: int) -> str:
+        return f"zero_pp_rank_{rank}_mp_rank_00_optim_states.pt"
+
     def save_checkpoint(self, save_dir: str, tag: str | None = None, client_state: dict | None = None):
-        """Collective like DeepSpeed's: every rank calls; rank 0 writes
-        <save_dir>/<tag>/mp_rank_00_model_states.pt and <save_dir>/latest, then all ranks
-        meet at a barrier.  [DS-UNVERIFIED layout, see SURVEY 8f-1]"""
+        """Collective like DeepSpeed's: every rank calls.  Rank 0 writes
+        <save_dir>/<tag>/mp_rank_00_model_states.pt (module tensors, stage-0 Adam state, counters)
+        and <save_dir>/latest; with zero_optimization.stage 1 EVERY rank also writes its own slice
+        of the Adam state as zero_pp_rank_<r>_mp_rank_00_optim_states.pt (DeepSpeed's naming), so
+        nothing of the optimizer is lost.  All ranks meet at a barrier before returning.
+        [DS-UNVERIFIED layout, see SURVEY 8f-1]"""
         tag = tag or f"global_step{self.global_steps}"
+        d = os.path.join(save_dir, tag)
+        os.makedirs(d, exist_ok=True)
+        groups = [{k: v for k, v in self.optimizer.param_groups[0].items() if k != "params"}]
+        if self.stage == 1:
+            shard = self.Ppad // self.le.world_size
+            torch.save({"zero_stage": 1, "rank": self.le.rank, "dp_world_size": self.le.world_size,
+                        "slice": (shard * self.le.rank, shard * (self.le.rank + 1)), "step": self.global_steps,
+                        "exp_avg": self.exp_avg.cpu(), "exp_avg_sq": self.exp_avg_sq.cpu(), "param_groups": groups},
+                       os.path.join(d, self._optim_file(self.le.rank)))
         if self.le.rank == 0:
-            d = os.path.join(save_dir, tag)
-            os.makedirs(d, exist_ok=True)
             flat = self.flat.detach().cpu()
             sd = {}
             names = dict((id(p), n) for n, p in self.module.named_parameters())
             for p, off, n in self._views:
                 sd[names[id(p)]] = flat[off:off + n].view(p.shape).clone()
+            opt = {"zero_stage": self.stage, "step": self.global_steps, "param_groups": groups}
+            if self.stage == 0:
+                m, v = self.exp_avg.cpu(), self.exp_avg_sq.cpu()
+                opt["exp_avg"] = {names[id(p)]: m[off:off + n].view(p.shape).clone() for p, off, n in self._views}
+                opt["exp_avg_sq"] = {names[id(p)]: v[off:off + n].view(p.shape).clone() for p, off, n in self._views}
             state = {
                 "module": sd,
-                "optimizer": {"exp_avg": self.exp_avg.cpu(), "exp_avg_sq": self.exp_avg_sq.cpu(), "zero_stage": self.stage,
-                              "step": self.global_steps, "param_groups": [
-                                  {k: v for k, v in self.optimizer.param_groups[0].items() if k != "params"}]},
+                "optimizer": opt,
                 "global_steps": self.global_steps,
                 "dp_world_size": self.le.world_size,
                 "client_state": client_state or {},
             }
-            torch.save(state, os.path.join(d, "mp_rank_00_model_states.pt"))
+            torch.save(state, os.path.join(d, self._MODEL_FILE))
             with open(os.path.join(save_dir, "latest"), "w") as f:
                 f.write(tag)
         _lib.check(self.lib.b200ds_barrier(self.ctx), "barrier")
         return True
+
+    def load_checkpoint(self, load_dir: str, tag: str | None = None, load_optimizer_states: bool = True):
+        """The load path the reference never exercises (it only saves, train.py:123-125): restores
+        what save_checkpoint wrote -- module tensors into the flat device buffer, Adam moments, the
+        step count -- so that the next step continues bit-for-bit.  Returns (path, client_state)
+        like DeepSpeed's engine, (None, None) when there is nothing to load."""
+        if tag is None:
+            latest = os.path.join(load_dir, "latest")
+            if not os.path.exists(latest):
+                return None, None
+            with open(latest) as f:
+                tag = f.read().strip()
+        d = os.path.join(load_dir, tag)
+        state = torch.load(os.path.join(d, self._MODEL_FILE), map_location="cpu", weights_only=False)
+        names = dict((id(p), n) for n, p in self.module.named_parameters())
+        for p, off, n in self._views:
+            t = state["module"][names[id(p)]]
+            if tuple(t.shape) != tuple(p.shape):
+                raise ValueError("load_checkpoint: %s has shape %s in the checkpoint, %s in the model"
+                                 % (names[id(p)], tuple(t.shape), tuple(p.shape)))
+            self.flat[off:off + n].copy_(t.reshape(-1).to(torch.float32))
+        if load_optimizer_states:
+            opt = state["optimizer"]
+            if int(opt["zero_stage"]) != self.stage or int(state["dp_world_size"]) != self.le.world_size and self.stage == 1:
+                raise ValueError("load_checkpoint: checkpoint was written with zero stage %s on %s ranks"
+                                 % (opt["zero_stage"], state["dp_world_size"]))
+            if self.stage == 0:
+                for p, off, n in self._views:
+                    self.exp_avg[off:off + n].copy_(opt["exp_avg"][names[id(p)]].reshape(-1))
+                    self.exp_avg_sq[off:off + n].copy_(opt["exp_avg_sq"][names[id(p)]].reshape(-1))
+            else:
+                mine = torch.load(os.path.join(d, self._optim_file(self.le.rank)), map_location="cpu", weights_only=False)
+                self.exp_avg.copy_(mine["exp_avg"])
+                self.exp_avg_sq.copy_(mine["exp_avg_sq"])
+            self.global_steps = int(opt["step"])
+            for t in self._step_tensors:
+                t.fill_(float(self.global_steps))
+        self._wq_step = -1                    # the bf16 operand pack is stale
+        _lib.check(self.lib.b200ds_barrier(self.ctx), "barrier")
+        return d, state.get("client_state", {})
 
     def destroy(self):
         self._finalizer()

@@ -136,6 +136,7 @@ int b200ds_ctx_destroy(b200ds_ctx* c) {
     }
     if (c->p2p_xchg[c->rank]) cudaFree(c->p2p_xchg[c->rank]);
     if (c->p2p_flags[c->rank]) cudaFree(c->p2p_flags[c->rank]);
+    if (c->p2p_mailbox) cudaFreeHost(c->p2p_mailbox);
   }
   if (c->ev_copied) cudaEventDestroy(c->ev_copied);
   if (c->comm) { const NcclApi* api = nccl_api(); if (api) api->CommDestroy(c->comm); }

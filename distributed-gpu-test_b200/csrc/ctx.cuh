@@ -36,6 +36,14 @@ struct b200ds_ctx {
   unsigned long long* p2p_flags[B200DS_P2P_MAX_WORLD] = {};
   int64_t p2p_cap = 0;               // floats per half of an exchange buffer; 0 = not enabled
   bool p2p_own = false;
+  // a kernel that gives up waiting for a peer reports here (pinned host memory, mapped into the device: it stays
+  // readable after the trap that follows): [0] = 1 + the rank waited for, [1] = the epoch
+  unsigned long long* p2p_mailbox = nullptr;       // host pointer
+  unsigned long long* p2p_mailbox_dev = nullptr;   // the same words as the device sees them
+  unsigned long long p2p_timeout_ns = 0;           // bound of a flag wait (B200DS_P2P_TIMEOUT_MS, default 300 s)
+  // host-batch prefetch: shape of the batch sitting in the staging half (a different shape is a miss)
+  int64_t pf_batch = 0;
+  int pf_F = 0;
 };
 
 namespace b200ds {

@@ -15,7 +15,9 @@ extern "C" {
 size_t b200ds_train_step_scratch_bytes(int64_t batch, int n_features, int hidden) {
   size_t f32 = b200ds_mlp_backward_f32_scratch_bytes(batch, n_features, hidden);
   size_t tcb = b200ds_mlp_backward_tc_scratch_bytes(batch, n_features, hidden);
-  return align_up(b200ds_bce_scratch_bytes(batch), 256) + align_up(f32 > tcb ? f32 : tcb, 256);
+  // [ loss scratch | backward scratch (fp32 or tensor-core) | forward slice parts + tile tickets (tensor-core, H > 2048) ]
+  return align_up(b200ds_bce_scratch_bytes(batch), 256) + align_up(f32 > tcb ? f32 : tcb, 256) +
+         align_up(b200ds_mlp_forward_tc_scratch_bytes(batch, n_features, hidden), 256);
 }
 
 // the device part of the step on staged inputs (x_dev, y_dev), loss left in b->loss
@@ -50,17 +52,19 @@ static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const flo
   if (use_tc) {
     if ((rc = b200ds_pack_x_bf16(x_dev, batch, n_features, b->xq, stream))) return rc;
     if ((rc = b200ds_pack_params_bf16(b->params, n_features, hidden, b->wq, stream))) return rc;
-    if ((rc = b200ds_mlp_forward_tc(b->xq, b->wq, b->params, batch, n_features, hidden, b->logits, stream))) return rc;
+    const size_t fwd_bytes = b200ds_mlp_forward_tc_scratch_bytes(batch, n_features, hidden);
+    if ((rc = b200ds_mlp_forward_tc(b->xq, b->wq, b->params, batch, n_features, hidden, b->logits,
+                                    fwd_bytes ? sc + need - align_up(fwd_bytes, 256) : nullptr, fwd_bytes, stream))) return rc;
   } else {
     if ((rc = b200ds_mlp_forward_f32(b->params, x_dev, batch, n_features, hidden, b->logits, stream))) return rc;
   }
   if (use_tc) {       // criterion + backward in one pass (dlogits is not materialised on this path)
     if ((rc = b200ds_mlp_loss_backward_tc(b->xq, b->wq, b->params, b->logits, y_dev, batch, n_features, hidden, b->loss,
-                                          b->grads, nullptr, sc + bce_bytes, b->scratch_bytes - bce_bytes, stream))) return rc;
+                                          b->grads, nullptr, sc + bce_bytes, need - bce_bytes - align_up(b200ds_mlp_forward_tc_scratch_bytes(batch, n_features, hidden), 256), stream))) return rc;
   } else {
     if ((rc = b200ds_bce_loss_grad(b->logits, y_dev, batch, b->loss, b->dlogits, nullptr, sc, bce_bytes, stream))) return rc;
     if ((rc = b200ds_mlp_backward_f32(b->params, x_dev, b->dlogits, batch, n_features, hidden, b->grads,
-                                      sc + bce_bytes, b->scratch_bytes - bce_bytes, stream))) return rc;
+                                      sc + bce_bytes, need - bce_bytes - align_up(b200ds_mlp_forward_tc_scratch_bytes(batch, n_features, hidden), 256), stream))) return rc;
   }
   if (ctx->world > 1 && ctx->p2p_cap >= Ppad)      // peer-memory exchange enabled on this context: one kernel for both
     return b200ds_allreduce_adam_p2p(ctx, b->params, b->grads, b->exp_avg, b->exp_avg_sq, Ppad, lr, beta1, beta2, eps,
@@ -152,7 +156,7 @@ int b200ds_train_step_host_prefetch(b200ds_ctx* ctx, const b200ds_step_bufs* b,
   }
   const size_t xb = sizeof(float) * (size_t)batch * n_features, yb = sizeof(float) * (size_t)batch;
   int slot;
-  if (ctx->pf_x == x_host && ctx->pf_y == y_host) {
+  if (ctx->pf_x == x_host && ctx->pf_y == y_host && ctx->pf_batch == batch && ctx->pf_F == n_features) {
     slot = ctx->pf_slot;                     // staged by the previous call: wait for that copy, not for a new one
     B200_CUDA(cudaStreamWaitEvent(s, ctx->ev_copied, 0));
   } else {
@@ -171,6 +175,7 @@ int b200ds_train_step_host_prefetch(b200ds_ctx* ctx, const b200ds_step_bufs* b,
     B200_CUDA(cudaMemcpyAsync(yn, y_next_host, yb, cudaMemcpyHostToDevice, ctx->copy));
     B200_CUDA(cudaEventRecord(ctx->ev_copied, ctx->copy));
     ctx->pf_x = x_next_host; ctx->pf_y = y_next_host; ctx->pf_slot = slot ^ 1;
+    ctx->pf_batch = batch; ctx->pf_F = n_features;      // the staged copy has THIS call's shape; a call with another shape re-copies
   }
   // the staged kernels as one graph replay (the one-launch tiny class stays eager)
   int rc = tiny_class(batch, n_features, hidden)

@@ -46,18 +46,20 @@ __device__ __forceinline__ size_t tiled_byte(int64_t row, int k) {
 
 // ------------------------------------------------------------------ packing
 // thread -> (row group, k chunk, row in group): consecutive threads write consecutive 16 B
+// rows [rows, batch) of the pack are padding: zero features (the ones columns stay, so such a row sees z1 = b1)
 __global__ void __launch_bounds__(256)
-pack_x_kernel(const float* __restrict__ x, int64_t batch, int F, uint4* __restrict__ xq) {
+pack_x_kernel(const float* __restrict__ x, int64_t rows, int64_t batch, int F, uint4* __restrict__ xq) {
   int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= batch * (KP / 8)) return;
   int r8 = (int)(t & 7), c = (int)((t >> 3) & 3);
   int64_t row = ((t >> 5) << 3) + r8;
   const float* xr = x + row * F;
+  const bool real = row < rows;
   __nv_bfloat16 v[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     int k = c * 8 + j;
-    float f = k < F ? xr[k] : (k < F + 2 ? 1.f : 0.f);
+    float f = k < F ? (real ? xr[k] : 0.f) : (k < F + 2 ? 1.f : 0.f);
     v[j] = __float2bfloat16(f);
   }
   xq[t] = *reinterpret_cast<uint4*>(v);
@@ -179,6 +181,7 @@ struct FwdSmem {                           // fixed-size tail after the W1 slice
   float red[2][4][64];                     // [column half][lane quadrant][column]: per-warp column sums
   uint64_t w_bar, x_full[kFwdXStages], x_free[kFwdXStages], d1_full[kFwdRing], d1_free[kFwdRing];
   uint32_t tmem_slot;
+  uint32_t last_of_tile;
 };
 
 // sum over the 32 lanes of 64 per-lane values; lane l ends with the totals of columns
@@ -200,7 +203,9 @@ template <int G>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __restrict__ w1q,
                   const float* __restrict__ vlin, const float* __restrict__ w2, const float* __restrict__ b2p,
-                  float* __restrict__ logits, int n_btiles, int slice_rows, int n_slices, int ctas_per_slice) {
+                  float* __restrict__ logits, float* __restrict__ zpart /* [n_slices][batch], n_slices > 1 */,
+                  unsigned int* __restrict__ tickets /* [n_btiles], zero between launches */,
+                  int n_btiles, int slice_rows, int n_slices, int ctas_per_slice) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slice = blockIdx.x % n_slices, cta_in_slice = blockIdx.x / n_slices;
@@ -215,7 +220,10 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
 
   if (threadIdx.x == 0) {
     mbar_init(&sh->w_bar, 1);
-    for (int i = 0; i < kFwdXStages; ++i) { mbar_init(&sh->x_full[i], 1); mbar_init(&sh->x_free[i], n_issuers); }
+    // an x stage has two kinds of readers: the MMAs (released by the issuers' tcgen05.commit) and the four
+    // half-0 epilogue warps, which read the tile's rows for the linear term -- both must be done with it
+    // before the producer may refill the stage (with NG <= RING the MMAs alone run a whole ring ahead)
+    for (int i = 0; i < kFwdXStages; ++i) { mbar_init(&sh->x_full[i], 1); mbar_init(&sh->x_free[i], n_issuers + 4); }
     for (int i = 0; i < kFwdRing; ++i) { mbar_init(&sh->d1_full[i], 1); mbar_init(&sh->d1_free[i], kFwdEpiWarps); }
     mbar_fence_init();
     // start the 128 KB W1 slice right away: it overlaps the rest of the prologue
@@ -309,7 +317,7 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
     const int half = warp >> 2, quad = warp & 3;
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     const int row = quad * 32 + lane;                      // the b row this thread finishes (half 0 warps only)
-    const float b2 = slice == 0 ? b2p[0] : 0.f;
+    const float b2 = b2p[0];
     int s = 0; uint32_t xph = 0; int gq = 0;
     for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice) {
       float lin = 0.f;
@@ -327,6 +335,8 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
             lin = fmaf(f.y, sh->v[c * 8 + 2 * j + 1], lin);
           }
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sh->x_free[s]);        // this warp's rows of the stage are in registers
       }
       if (++s == kFwdXStages) { s = 0; xph ^= 1; }
       float acc[64];
@@ -383,10 +393,28 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
       if (half == 0) {
         const int hb = row >> 6, cb = row & 63;
         const float ab = (sh->red[hb][0][cb] + sh->red[hb][1][cb]) + (sh->red[hb][2][cb] + sh->red[hb][3][cb]);
-        const float z = 0.5f * (lin + ab) + b2;
-        float* dst = logits + (size_t)t * kTileRows + row;
-        if (n_slices == 1) *dst = z;
-        else atomicAdd(dst, z);
+        const float z = 0.5f * (lin + ab);
+        const size_t gi = (size_t)t * kTileRows + row;
+        if (n_slices == 1) {
+          logits[gi] = z + b2;
+        } else {
+          // Several slices of hidden units add into one logit.  Each writes its part; the CTA that finishes the
+          // tile LAST (one ticket per tile) sums the parts in slice order, so the result does not depend on which
+          // slice was faster: bit-reproducible run to run, and no zeroing of the logits beforehand.
+          const size_t nrows = (size_t)n_btiles * kTileRows;
+          __stcg(zpart + (size_t)slice * nrows + gi, z);
+          __threadfence();
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+          if (threadIdx.x == 0) sh->last_of_tile = atomicAdd(&tickets[t], 1u) == (unsigned)(n_slices - 1);
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+          if (sh->last_of_tile) {
+            __threadfence();
+            float zs = __ldcg(zpart + gi);
+            for (int sl = 1; sl < n_slices; ++sl) zs += __ldcg(zpart + (size_t)sl * nrows + gi);
+            logits[gi] = zs + b2;
+            if (threadIdx.x == 0) tickets[t] = 0u;
+          }
+        }
       }
     }
   }
@@ -821,13 +849,7 @@ mlp_update_tc_kernel(const float* __restrict__ partial, const float* __restrict_
       st_release_sys(&d.flags[threadIdx.x][d.rank], e);
       if (threadIdx.x == 0) d.tickets[0] = 0u;
     }
-    if (threadIdx.x < d.world) {
-      const unsigned long long* f = &d.flags[d.rank][threadIdx.x];
-      unsigned long long spins = 0;
-      while (ld_acquire_sys(f) < e) {
-        if (++spins > (1ull << 26)) __trap();
-      }
-    }
+    if (threadIdx.x < d.world) p2p_wait_flag(&d.flags[d.rank][threadIdx.x], e, (int)threadIdx.x, d);
     __syncthreads();
     float4 lo4 = make_float4(0.f, 0.f, 0.f, 0.f), hi4 = lo4;
     float sb2 = 0.f;
@@ -962,14 +984,20 @@ size_t b200ds_tc_xq_bytes(int64_t batch) { return batch > 0 ? (size_t)batch * KP
 
 size_t b200ds_tc_wq_bytes(int hidden) { return hidden > 0 ? (size_t)hidden * KP * 2 + (size_t)(hidden / kPackRows) * 32 * sizeof(float) : 0; }
 
-int b200ds_pack_x_bf16(const float* x_dev, int64_t batch, int n_features, void* xq_dev, uintptr_t stream) {
+int b200ds_pack_x_bf16_rows(const float* x_dev, int64_t rows, int64_t batch, int n_features, void* xq_dev, uintptr_t stream) {
   B200_REQUIRE(batch > 0 && batch % 8 == 0, "pack_x_bf16: batch must be a positive multiple of 8 (got %lld)", (long long)batch);
+  B200_REQUIRE(rows >= 0 && rows <= batch, "pack_x_bf16: rows (%lld) must be in [0, batch = %lld]", (long long)rows, (long long)batch);
   B200_REQUIRE(n_features >= 1 && n_features + 2 <= KP, "pack_x_bf16: F must be in [1,%d] (got %d)", KP - 2, n_features);
   B200_REQUIRE(x_dev && xq_dev, "pack_x_bf16: null pointer");
   int64_t threads = batch * (KP / 8);
-  pack_x_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, as_stream(stream)>>>(x_dev, batch, n_features, reinterpret_cast<uint4*>(xq_dev));
+  pack_x_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, as_stream(stream)>>>(x_dev, rows, batch, n_features,
+                                                                                  reinterpret_cast<uint4*>(xq_dev));
   B200_LAUNCH_CHECK();
   return B200DS_OK;
+}
+
+int b200ds_pack_x_bf16(const float* x_dev, int64_t batch, int n_features, void* xq_dev, uintptr_t stream) {
+  return b200ds_pack_x_bf16_rows(x_dev, batch, batch, n_features, xq_dev, stream);
 }
 
 static int launch_gen_batch(void* xq_dev, float* y_dev, int64_t batch, int n_features, uint64_t seed, uint64_t offset,
@@ -1031,8 +1059,15 @@ int b200ds_pack_params_bf16(const float* params_dev, int n_features, int hidden,
   return B200DS_OK;
 }
 
+size_t b200ds_mlp_forward_tc_scratch_bytes(int64_t batch, int n_features, int hidden) {
+  FwdPlan fp;
+  if (!tc_shape_ok(batch, n_features, hidden) || !fwd_plan(batch, hidden, &fp) || fp.slices == 1) return 0;
+  return (size_t)fp.slices * (size_t)batch * sizeof(float) + (size_t)fp.n_btiles * sizeof(unsigned int);
+}
+
 int b200ds_mlp_forward_tc(const void* xq_dev, const void* wq_dev, const float* params_dev, int64_t batch,
-                          int n_features, int hidden, float* logits_dev, uintptr_t stream) {
+                          int n_features, int hidden, float* logits_dev, void* scratch_dev, size_t scratch_bytes,
+                          uintptr_t stream) {
   B200_REQUIRE(tc_shape_ok(batch, n_features, hidden),
                "mlp_forward_tc: needs F <= %d, H %% 128 == 0, batch %% 128 == 0 (got B=%lld F=%d H=%d)", KP - 2,
                (long long)batch, n_features, hidden);
@@ -1049,13 +1084,16 @@ int b200ds_mlp_forward_tc(const void* xq_dev, const void* wq_dev, const float* p
     B200_CUDA(cudaFuncSetAttribute(mlp_fwd_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set[dev & 63] = true;
   }
-  if (fp.slices > 1) B200_CUDA(cudaMemsetAsync(logits_dev, 0, sizeof(float) * batch, st));
+  const size_t need = b200ds_mlp_forward_tc_scratch_bytes(batch, n_features, hidden);
+  B200_REQUIRE(need == 0 || (scratch_dev && scratch_bytes >= need), "mlp_forward_tc: scratch too small (%zu < %zu)", scratch_bytes, need);
+  float* zpart = reinterpret_cast<float*>(scratch_dev);
+  unsigned int* tickets = need ? reinterpret_cast<unsigned int*>(zpart + (size_t)fp.slices * batch) : nullptr;
   const unsigned char* w1q = reinterpret_cast<const unsigned char*>(wq_dev);
   const float* v = reinterpret_cast<const float*>(w1q + (size_t)hidden * KP * 2);
   auto kern = (fp.slice_rows / kTileRows) % 2 == 0 ? mlp_fwd_tc_kernel<2> : mlp_fwd_tc_kernel<1>;
   kern<<<fp.slices * fp.ctas_per_slice, kFwdThreads, fp.smem, st>>>(
       reinterpret_cast<const unsigned char*>(xq_dev), w1q, v, params_dev + L.off_w2(), params_dev + L.off_b2(), logits_dev,
-      fp.n_btiles, fp.slice_rows, fp.slices, fp.ctas_per_slice);
+      zpart, tickets, fp.n_btiles, fp.slice_rows, fp.slices, fp.ctas_per_slice);
   B200_LAUNCH_CHECK();
   return B200DS_OK;
 }

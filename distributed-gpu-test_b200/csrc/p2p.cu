@@ -20,6 +20,7 @@
 #include "ctx.cuh"
 #include "p2p.cuh"
 #include <string.h>
+#include <stdlib.h>
 
 namespace b200ds {
 
@@ -61,14 +62,8 @@ p2p_allreduce_adam_kernel(float* __restrict__ p, float* __restrict__ g, float* _
     sh[0] = (float)(-(lr / bc1));
     sh[1] = (float)sqrt(bc2);
   }
-  // ---- 2. wait for every rank's publication (bounded: a protocol bug traps instead of hanging the box)
-  if (threadIdx.x < d.world) {
-    const unsigned long long* f = &d.flags[d.rank][threadIdx.x];
-    unsigned long long spins = 0;
-    while (ld_acquire_sys(f) < e) {
-      if (++spins > (1ull << 26)) __trap();
-    }
-  }
+  // ---- 2. wait for every rank's publication (bounded in wall time, see p2p_wait_flag)
+  if (threadIdx.x < d.world) p2p_wait_flag(&d.flags[d.rank][threadIdx.x], e, (int)threadIdx.x, d);
   __syncthreads();
   // ---- 3. sum in rank order, Adam
   const float neg_step_size = sh[0], bc2_sqrt = sh[1];
@@ -114,6 +109,36 @@ struct P2PHandles {
 
 extern "C" {
 
+// Undo whatever part of the set-up exists: close the peers' mappings, free the local buffers.
+static void p2p_teardown(b200ds_ctx* ctx) {
+  for (int w = 0; w < ctx->world && w < B200DS_P2P_MAX_WORLD; ++w) {
+    if (w == ctx->rank) continue;
+    if (ctx->p2p_xchg[w]) cudaIpcCloseMemHandle(ctx->p2p_xchg[w]);
+    if (ctx->p2p_flags[w]) cudaIpcCloseMemHandle(ctx->p2p_flags[w]);
+    ctx->p2p_xchg[w] = nullptr; ctx->p2p_flags[w] = nullptr;
+  }
+  if (ctx->p2p_xchg[ctx->rank]) cudaFree(ctx->p2p_xchg[ctx->rank]);
+  if (ctx->p2p_flags[ctx->rank]) cudaFree(ctx->p2p_flags[ctx->rank]);
+  ctx->p2p_xchg[ctx->rank] = nullptr; ctx->p2p_flags[ctx->rank] = nullptr;
+  if (ctx->p2p_mailbox) cudaFreeHost(ctx->p2p_mailbox);
+  ctx->p2p_mailbox = ctx->p2p_mailbox_dev = nullptr;
+  ctx->p2p_own = false;
+  ctx->p2p_cap = 0;
+  cudaGetLastError();
+}
+
+// The local half of the set-up; on failure the caller still takes part in the vote below.
+static int p2p_local_setup(b200ds_ctx* ctx, int64_t cap, void** words) {
+  B200_CUDA(cudaMalloc(&ctx->p2p_xchg[ctx->rank], sizeof(float) * 2 * (size_t)cap));
+  B200_CUDA(cudaMalloc(words, 256));      // flag row (W x u64) | epoch (u64) | tickets (2 x u32)
+  ctx->p2p_flags[ctx->rank] = reinterpret_cast<unsigned long long*>(*words);
+  B200_CUDA(cudaMemset(*words, 0, 256));
+  B200_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&ctx->p2p_mailbox), 2 * sizeof(unsigned long long), cudaHostAllocMapped));
+  ctx->p2p_mailbox[0] = ctx->p2p_mailbox[1] = 0ull;
+  B200_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&ctx->p2p_mailbox_dev), ctx->p2p_mailbox, 0));
+  return B200DS_OK;
+}
+
 int b200ds_ctx_enable_p2p(b200ds_ctx* ctx, int64_t max_elems) {
   B200_REQUIRE(ctx != nullptr, "ctx_enable_p2p: null context");
   B200_REQUIRE(max_elems > 0, "ctx_enable_p2p: max_elems must be positive");
@@ -123,34 +148,47 @@ int b200ds_ctx_enable_p2p(b200ds_ctx* ctx, int64_t max_elems) {
   B200_CUDA(cudaSetDevice(ctx->device));
   const int W = ctx->world;
   const int64_t cap = (max_elems + 3) / 4 * 4;
-  B200_CUDA(cudaMalloc(&ctx->p2p_xchg[ctx->rank], sizeof(float) * 2 * (size_t)cap));
-  void* words = nullptr;                              // flag row (W x u64) | epoch (u64) | tickets (2 x u32), 256 bytes
-  B200_CUDA(cudaMalloc(&words, 256));
-  B200_CUDA(cudaMemset(words, 0, 256));
-  ctx->p2p_flags[ctx->rank] = reinterpret_cast<unsigned long long*>(words);
+  {
+    const char* ms = getenv("B200DS_P2P_TIMEOUT_MS");
+    long long v = ms ? atoll(ms) : 0;
+    ctx->p2p_timeout_ns = (unsigned long long)(v > 0 ? v : 300000) * 1000000ull;
+  }
+  void* words = nullptr;
   ctx->p2p_own = true;
+  int my_rc = p2p_local_setup(ctx, cap, &words);
+  char my_err[256];
+  snprintf(my_err, sizeof(my_err), "%s", my_rc ? b200ds_last_error() : "");
   if (W > 1) {
+    // The outcome is COLLECTIVE: a rank that cannot map a peer must not leave the others enabled (their next
+    // exchange would wait for a publication that never comes).  Every rank therefore walks the same sequence of
+    // communicator calls whatever happens locally, and the last one sums a failure flag over all ranks.
     const NcclApi* api = nccl_api();
-    if (!api) return B200DS_ERR_NCCL;
-    if (!ctx->comm) { set_error("ctx_enable_p2p: context has no communicator"); return B200DS_ERR_STATE; }
-    P2PHandles mine;
-    B200_CUDA(cudaIpcGetMemHandle(&mine.xchg, ctx->p2p_xchg[ctx->rank]));
-    B200_CUDA(cudaIpcGetMemHandle(&mine.flags, words));
+    if (!api) { p2p_teardown(ctx); return B200DS_ERR_NCCL; }
+    if (!ctx->comm) { p2p_teardown(ctx); set_error("ctx_enable_p2p: context has no communicator"); return B200DS_ERR_STATE; }
     static_assert(sizeof(P2PHandles) == 128, "two IPC handles");
+    P2PHandles mine;
+    memset(&mine, 0, sizeof(mine));
+    if (!my_rc) {
+      cudaError_t e = cudaIpcGetMemHandle(&mine.xchg, ctx->p2p_xchg[ctx->rank]);
+      if (e == cudaSuccess) e = cudaIpcGetMemHandle(&mine.flags, words);
+      if (e != cudaSuccess) { my_rc = cuda_fail(e, "cudaIpcGetMemHandle", __FILE__, __LINE__); snprintf(my_err, sizeof(my_err), "%s", b200ds_last_error()); }
+    }
     unsigned char* gather = nullptr;
-    B200_CUDA(cudaMalloc(&gather, sizeof(P2PHandles) * (size_t)W));
-    B200_CUDA(cudaMemcpy(gather + sizeof(P2PHandles) * (size_t)ctx->rank, &mine, sizeof(mine), cudaMemcpyHostToDevice));
+    P2PHandles all[B200DS_P2P_MAX_WORLD];
+    cudaError_t ge = cudaMalloc(&gather, sizeof(P2PHandles) * (size_t)W);
+    if (ge != cudaSuccess) { p2p_teardown(ctx); return cuda_fail(ge, "cudaMalloc(handle gather)", __FILE__, __LINE__); }   // nothing collective can run without it
+    cudaMemcpy(gather + sizeof(P2PHandles) * (size_t)ctx->rank, &mine, sizeof(mine), cudaMemcpyHostToDevice);
     ncclResult_t r = api->AllGather(gather + sizeof(P2PHandles) * (size_t)ctx->rank, gather, sizeof(P2PHandles), ncclChar, ctx->comm,
                                     ctx->side);
-    if (r != ncclSuccess) { cudaFree(gather); set_error("ctx_enable_p2p: ncclAllGather failed (%s)", api->GetErrorString(r)); return B200DS_ERR_NCCL; }
-    B200_CUDA(cudaStreamSynchronize(ctx->side));
-    P2PHandles all[B200DS_P2P_MAX_WORLD];
-    B200_CUDA(cudaMemcpy(all, gather, sizeof(P2PHandles) * (size_t)W, cudaMemcpyDeviceToHost));
-    B200_CUDA(cudaFree(gather));
-    // A rank that cannot map a peer (no peer access between the two devices, device not visible to
-    // this process) must still reach the barrier below, or the others would wait for it forever.
-    int map_rc = B200DS_OK;
-    for (int w = 0; w < W && map_rc == B200DS_OK; ++w) {
+    cudaError_t se = cudaStreamSynchronize(ctx->side);
+    if (r == ncclSuccess && se == cudaSuccess) se = cudaMemcpy(all, gather, sizeof(P2PHandles) * (size_t)W, cudaMemcpyDeviceToHost);
+    cudaFree(gather);
+    if (r != ncclSuccess || se != cudaSuccess) {
+      p2p_teardown(ctx);
+      if (r != ncclSuccess) { set_error("ctx_enable_p2p: ncclAllGather failed (%s)", api->GetErrorString(r)); return B200DS_ERR_NCCL; }
+      return cuda_fail(se, "handle exchange", __FILE__, __LINE__);
+    }
+    for (int w = 0; w < W && my_rc == B200DS_OK; ++w) {
       if (w == ctx->rank) continue;
       void* px = nullptr; void* pf = nullptr;
       cudaError_t e = cudaIpcOpenMemHandle(&px, all[w].xchg, cudaIpcMemLazyEnablePeerAccess);
@@ -162,16 +200,40 @@ int b200ds_ctx_enable_p2p(b200ds_ctx* ctx, int64_t max_elems) {
         ctx->p2p_flags[w] = reinterpret_cast<unsigned long long*>(pf);
       } else {
         cudaGetLastError();
-        set_error("ctx_enable_p2p: cannot map rank %d's exchange buffer: %s", w, cudaGetErrorString(e));
-        map_rc = B200DS_ERR_CUDA;
+        snprintf(my_err, sizeof(my_err), "ctx_enable_p2p: cannot map rank %d's exchange buffer: %s", w, cudaGetErrorString(e));
+        my_rc = B200DS_ERR_CUDA;
       }
     }
-    // nobody may publish before every rank has opened every mapping and zeroed its words
-    int rc = b200ds_barrier(ctx);
-    if (map_rc) return map_rc;
-    if (rc) return rc;
+    // the vote; it is also the barrier after which a rank may publish (every mapping is open, every word zeroed)
+    float vote = my_rc ? 1.f : 0.f, total = 1.f;
+    cudaError_t ve = cudaMemcpy(ctx->barrier_word + 1, &vote, sizeof(float), cudaMemcpyHostToDevice);
+    r = api->AllReduce(ctx->barrier_word + 1, ctx->barrier_word + 1, 1, ncclFloat32, ncclSum, ctx->comm, ctx->side);
+    if (ve == cudaSuccess) ve = cudaStreamSynchronize(ctx->side);
+    if (ve == cudaSuccess && r == ncclSuccess) ve = cudaMemcpy(&total, ctx->barrier_word + 1, sizeof(float), cudaMemcpyDeviceToHost);
+    if (r != ncclSuccess || ve != cudaSuccess || total != 0.f) {
+      p2p_teardown(ctx);
+      if (my_rc) { set_error("%s", my_err); return my_rc; }
+      if (r != ncclSuccess) { set_error("ctx_enable_p2p: ncclAllReduce failed (%s)", api->GetErrorString(r)); return B200DS_ERR_NCCL; }
+      if (ve != cudaSuccess) return cuda_fail(ve, "set-up vote", __FILE__, __LINE__);
+      set_error("ctx_enable_p2p: %d rank(s) could not map their peers; the peer-memory exchange stays off on every rank", (int)total);
+      return B200DS_ERR_STATE;
+    }
+  } else if (my_rc) {
+    p2p_teardown(ctx);
+    set_error("%s", my_err);
+    return my_rc;
   }
   ctx->p2p_cap = cap;
+  return B200DS_OK;
+}
+
+// A wait that timed out in an earlier launch left a note in the mailbox (and a trapped context).
+static int p2p_check_mailbox(const b200ds_ctx* ctx, const char* who) {
+  if (ctx->p2p_mailbox && ctx->p2p_mailbox[0] != 0ull) {
+    set_error("%s: an earlier exchange on rank %d gave up waiting for rank %d at epoch %llu (B200DS_P2P_TIMEOUT_MS = %llu)", who,
+              ctx->rank, (int)(ctx->p2p_mailbox[0] - 1ull), ctx->p2p_mailbox[1], ctx->p2p_timeout_ns / 1000000ull);
+    return B200DS_ERR_STATE;
+  }
   return B200DS_OK;
 }
 
@@ -186,6 +248,7 @@ int b200ds_allreduce_adam_p2p(b200ds_ctx* ctx, float* params_dev, float* grads_d
   B200_REQUIRE(((((uintptr_t)params_dev) | ((uintptr_t)grads_dev) | ((uintptr_t)exp_avg_dev) | ((uintptr_t)exp_avg_sq_dev)) & 15) == 0,
                "allreduce_adam_p2p: buffers must be 16-byte aligned");
   B200_REQUIRE(step_counter_dev != nullptr || step >= 1, "allreduce_adam_p2p: step must be >= 1 (t after the increment)");
+  if (int rc = p2p_check_mailbox(ctx, "allreduce_adam_p2p")) return rc;
   const P2PDev d = make_p2p_dev(ctx);
   const AdamScalars s = make_adam_scalars(beta1, beta2, eps, ctx->world > 1 ? (float)(1.0 / ctx->world) : 1.f);
   // every CTA spins in phase 2, so all of them must be resident at once: at most one CTA per SM

@@ -13,7 +13,15 @@ struct P2PDev {
   unsigned long long* flags[B200DS_P2P_MAX_WORLD];   // every rank's flag row: flags[p][r] = last epoch rank r published to p
   unsigned long long* epoch;                // local: epochs completed
   unsigned int* tickets;                    // local: [0] copy-phase arrivals, [1] exit arrivals
+  unsigned long long timeout_ns;            // bound of one flag wait
+  unsigned long long* mailbox;              // pinned host words a timed-out wait reports into before it traps
 };
+
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
   unsigned long long v;
@@ -30,6 +38,12 @@ __device__ __forceinline__ float4 ld_peer(const float4* p) {
   return v;
 }
 
+// Wait until *flag >= e.  Ranks drift apart by far more than a spin count covers (first-call module load, a graph
+// capture, rank 0 writing a checkpoint), so the bound is wall time on %globaltimer, generous and configurable.  A
+// wait that still runs out says which rank it waited for in the pinned mailbox (readable by the host after the
+// trap) and traps: a hang would take the box down with it.
+__device__ __forceinline__ void p2p_wait_flag(const unsigned long long* flag, unsigned long long e, int peer, const struct P2PDev& d);
+
 // words of the local flag allocation: flag row (MAX_WORLD x u64) | epoch (u64) | tickets (2 x u32)
 inline P2PDev make_p2p_dev(const b200ds_ctx* ctx) {
   P2PDev d;
@@ -41,7 +55,25 @@ inline P2PDev make_p2p_dev(const b200ds_ctx* ctx) {
     d.epoch = words + B200DS_P2P_MAX_WORLD;
     d.tickets = reinterpret_cast<unsigned int*>(words + B200DS_P2P_MAX_WORLD + 1);
   }
+  d.timeout_ns = ctx->p2p_timeout_ns;
+  d.mailbox = ctx->p2p_mailbox_dev;
   return d;
+}
+
+__device__ __forceinline__ void p2p_wait_flag(const unsigned long long* flag, unsigned long long e, int peer, const P2PDev& d) {
+  if (ld_acquire_sys(flag) >= e) return;
+  const unsigned long long t0 = global_timer_ns();
+  unsigned int polls = 0;
+  while (ld_acquire_sys(flag) < e) {
+    if ((++polls & 1023u) == 0 && global_timer_ns() - t0 > d.timeout_ns) {
+      if (d.mailbox) {
+        d.mailbox[1] = e;
+        d.mailbox[0] = 1ull + (unsigned long long)peer;
+        __threadfence_system();
+      }
+      __trap();
+    }
+  }
 }
 
 }  // namespace b200ds

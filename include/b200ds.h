@@ -201,6 +201,12 @@ B200DS_API size_t b200ds_tc_xq_bytes(int64_t batch);
 B200DS_API size_t b200ds_tc_wq_bytes(int hidden);
 B200DS_API int b200ds_pack_x_bf16(const float* x_dev, int64_t batch, int n_features, void* xq_dev,
                                   uintptr_t stream);
+/* Same with a batch padded up to the shape class: x holds `rows` real rows, the pack gets `batch`
+ * rows (batch % 8 == 0), rows [rows, batch) with zero features.  The engine uses it to run the
+ * reference's own tiny batches (train.py:74, 4 rows, ragged tail) through the bf16 kernels; the
+ * padded rows must be given dlogits = 0 in the backward. */
+B200DS_API int b200ds_pack_x_bf16_rows(const float* x_dev, int64_t rows, int64_t batch, int n_features,
+                                       void* xq_dev, uintptr_t stream);
 /* Generated-batch configs: draw the batch and write it straight into the pack, with its
  * labels -- xq[b,k] = bf16(x[b,k]) where x = torch.randn(batch*F, device='cuda') under
  * (seed, offset) viewed as [batch,F] (same stream and mapping as b200ds_philox_normal), and
@@ -216,10 +222,15 @@ B200DS_API int b200ds_gen_batch_bf16_counted(void* xq_dev, float* y_dev, int64_t
 B200DS_API int b200ds_pack_params_bf16(const float* params_dev, int n_features, int hidden, void* wq_dev,
                                        uintptr_t stream);
 /* model_engine(batch_x) (train.py:107): logits[b] = relu(xq[b,:] . w1q[n,:]) . W2 + b2, the
- * hidden activation stays in TMEM/registers.  W2 and b2 are read in fp32 from params_dev. */
+ * hidden activation stays in TMEM/registers.  W2 and b2 are read in fp32 from params_dev.
+ * H > 2048 is split into slices of hidden units handled by different CTAs; their parts of a logit
+ * are summed in slice order through `scratch` (b200ds_mlp_forward_tc_scratch_bytes; 0 bytes and a
+ * NULL pointer for H <= 2048; zeroed once by the caller, left zeroed by every call), so the
+ * result is bit-reproducible from run to run for every H. */
+B200DS_API size_t b200ds_mlp_forward_tc_scratch_bytes(int64_t batch, int n_features, int hidden);
 B200DS_API int b200ds_mlp_forward_tc(const void* xq_dev, const void* wq_dev, const float* params_dev,
                                      int64_t batch, int n_features, int hidden, float* logits_dev,
-                                     uintptr_t stream);
+                                     void* scratch_dev, size_t scratch_bytes, uintptr_t stream);
 /* model_engine.backward(loss) up to the all-reduce (train.py:113): recomputes the
  * activation mask on the tensor cores, accumulates S[n,k] = sum_b 1[z1[b,n]>0] dz[b] xq[b,k]
  * in TMEM, then dW1 = W2[n] S[n,:F], db1 = W2[n] S[n,F], dW2[n] = sum_k w1q[n,k] S[n,k],
@@ -316,7 +327,10 @@ B200DS_API int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* b
  * (x_host, y_host) are the pointers given as (x_next_host, y_next_host) by the previous call
  * uses the staged copy and copies nothing; any other pointers are copied as in
  * b200ds_train_step_host.  A prefetched host buffer must stay unchanged until the call that
- * consumes it returns.  NULL next pointers = no prefetch.  Result per call: identical to
+ * consumes it returns.  NULL next pointers = no prefetch.  The announced batch is copied with THIS
+ * call's batch and n_features, so it must have the same shape (do not announce a ragged last
+ * batch: pass NULL); a consuming call whose shape differs from the staged one ignores the staged
+ * copy and copies its own inputs.  Result per call: identical to
  * b200ds_train_step_host on the same batch.  The device part of the step is captured once per
  * (buffers, staging half, shape, hyper-parameters) as a CUDA graph on a stream of the context and
  * replayed on the caller's stream (one launch per step instead of ~8); the graphs are destroyed

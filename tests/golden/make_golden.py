@@ -117,7 +117,7 @@ def main():
         "torch_version": np.array([torch.__version__]),
         "cpu_capability": np.array([torch.backends.cpu.get_cpu_capability()]),
     }
-    for world, epochs in ((1, 5), (2, 5), (8, 5)):
+    for world, epochs in ((1, 5), (2, 5), (4, 5), (8, 5)):
         r = run_reference(ref, world, epochs)
         tag = f"w{world}"
         if world == 1:

@@ -1,0 +1,166 @@
+"""Parity of EXACTLY what bench.py times, at the sizes it times it (BASELINE config 4:
+wide4096 / wide8192, 65536 samples per GPU): the device-resident step of bench.WideStep --
+gen_batch_bf16_counted -> mlp_forward_tc -> mlp_loss_backward_tc (+finish) -> adam_step_counted ->
+pack_params_bf16, driven by device counters -- run for N consecutive steps, once as eager launches
+and once as ONE captured CUDA graph replayed N times (the form the timed region uses).
+
+Checked (train.py:104-117 for N steps; north_star: "batches bit-exact, loss and parameters within
+2e-2 after N steps for bf16"):
+  * the batch of step k is the k-th consecutive torch.randn(B*F, device='cuda') draw under the same
+    seed, bit for bit, after the same bf16 pack -- through the fused generator, eager and replayed;
+  * eager and graph-replayed runs end in the same bits (loss of every step, parameters, Adam state);
+  * the same N steps through the fp32 kernels (same batches: same Philox stream) agree on every
+    step's loss within 2e-2, and on the parameters element by element (see _assert_params).
+"""
+import ctypes as C
+
+import pytest
+import torch
+
+import bench
+
+pytestmark = pytest.mark.gpu
+
+N_STEPS = 20
+
+
+def _note(d):
+    """diagnostics next to the verdict (kept when the run happens under gpurun)"""
+    import json
+    import os
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "bench_path_parity.jsonl"), "a") as f:
+            f.write(json.dumps(d) + "\n")
+
+
+def _ctx(lib):
+    from b200ds import _lib
+    ctx = C.c_void_p()
+    _lib.check(lib.b200ds_ctx_create(0, 0, 1, None, C.byref(ctx)))
+    return ctx
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _expected_packs(lib, dev, wl, seed, n):
+    """bf16 packs + labels of the first n consecutive torch.randn draws of torch's own CUDA generator."""
+    from b200ds import _lib
+    B, F = wl["B"], wl["F"]
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    out = []
+    for _ in range(n):
+        x = torch.randn(B * F, device=dev, generator=g)
+        xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=dev)
+        _lib.check(lib.b200ds_pack_x_bf16(x.data_ptr(), B, F, xq.data_ptr(), _st()))
+        y = (x.view(B, F)[:, : F // 2].sum(dim=1) > 0).float()
+        out.append((xq, y, x))
+    return out
+
+
+def _run_bf16(lib, dev, wl, n, graph):
+    """n steps of bench.WideStep (bf16).  Returns per-step losses, the batch each step consumed, final state."""
+    ctx = _ctx(lib)
+    ws = bench.WideStep(lib, ctx, dev, wl, 1, 0, "bf16")
+    losses, packs = [], []
+    st = _st()
+    if not graph:
+        for k in range(n):
+            if k == 0:
+                ws.step(st)              # primes batch 0 itself; what it consumed is checked through the graph run and step 1..
+                torch.cuda.synchronize()
+                packs.append(None)
+            else:
+                packs.append((ws.xq.clone(), ws.y.clone()))
+                ws.step(st)
+            torch.cuda.synchronize()
+            losses.append(float(ws.loss))
+    else:
+        ws.step(st)                       # step 0 eagerly (primes the first batch and the weight pack), then capture
+        torch.cuda.synchronize()
+        losses.append(float(ws.loss))
+        packs.append(None)
+        g = torch.cuda.CUDAGraph()
+        cap = torch.cuda.Stream(device=dev)
+        cap.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.graph(g, stream=cap):
+            ws.step(torch.cuda.current_stream().cuda_stream)
+        torch.cuda.current_stream().wait_stream(cap)
+        for k in range(1, n):
+            packs.append((ws.xq.clone(), ws.y.clone()))
+            g.replay()
+            torch.cuda.synchronize()
+            losses.append(float(ws.loss))
+        g.reset()
+    state = dict(params=ws.params.clone(), m=ws.m.clone(), v=ws.v.clone(), counter=int(ws.counter), seed=ws.seed, P=ws.P)
+    from b200ds import _lib
+    _lib.check(lib.b200ds_ctx_destroy(ctx))
+    return losses, packs, state
+
+
+def _run_fp32(lib, dev, wl, n):
+    ctx = _ctx(lib)
+    ws = bench.WideStep(lib, ctx, dev, wl, 1, 0, "fp32")
+    losses, xs = [], []
+    for k in range(n):
+        ws.step(_st())
+        torch.cuda.synchronize()
+        losses.append(float(ws.loss))
+        xs.append(ws.x.clone() if k < 3 else None)
+    state = dict(params=ws.params.clone(), P=ws.P)
+    from b200ds import _lib
+    _lib.check(lib.b200ds_ctx_destroy(ctx))
+    return losses, xs, state
+
+
+def _assert_params(p16, p32, p0, n_steps, lr, F, H):
+    """Element by element.  Adam moves a parameter by at most ~lr per step whatever the size of its gradient, and
+    the direction of that move is the SIGN of a ratio of noisy sums: where a gradient is smaller than its own bf16
+    error the two paths may step in different directions.  So every element is held to
+         |p16 - p32| <= 2e-2 * |p32 - p0| + 2e-2 * n_steps * lr          (2 % of the move, plus 2 % of the reach),
+    with at most one element in a thousand outside it, and NO element further than the reach itself
+    (2 * n_steps * lr: opposite directions on every step)."""
+    d = (p16.double() - p32.double()).abs()
+    reach = n_steps * lr
+    bound = 2e-2 * (p32.double() - p0.double()).abs() + 2e-2 * reach
+    frac = float((d > bound).double().mean())
+    rels = {}
+    for name, o, n in (("w1", 0, H * F), ("b1", H * F, H), ("w2", H * F + H, H), ("b2", H * F + 2 * H, 1)):
+        move = (p32[o:o + n].double() - p0[o:o + n].double())
+        rels[name] = float((p16[o:o + n].double() - p32[o:o + n].double()).norm() / max(1e-30, float(move.norm())))
+    _note(dict(H=H, frac_outside=frac, max_abs_diff=float(d.max()), reach=reach, group_rel=rels))
+    assert frac <= 1e-3, frac
+    assert float(d.max()) <= 2 * reach, float(d.max())
+    for name, rel in rels.items():
+        assert rel <= 2e-2, (name, rel)          # the step taken by each group as a whole: within 2 %
+
+
+@pytest.mark.parametrize("workload", ["wide4096", "wide8192"])
+def test_bench_sequence_n_steps_eager_graph_fp32(lib, cuda_dev, workload):
+    wl = bench.WORKLOADS[workload]
+    B, F, H = wl["B"], wl["F"], wl["H"]
+    l_eager, packs_eager, s_eager = _run_bf16(lib, cuda_dev, wl, N_STEPS, graph=False)
+    l_graph, packs_graph, s_graph = _run_bf16(lib, cuda_dev, wl, N_STEPS, graph=True)
+    # (1) step k consumed the k-th consecutive torch.randn draw (k >= 1 observed directly; k = 0 through the loss below)
+    exp = _expected_packs(lib, cuda_dev, wl, s_eager["seed"], N_STEPS)
+    for k in range(1, N_STEPS):
+        for packs in (packs_eager, packs_graph):
+            assert torch.equal(packs[k][0], exp[k][0]), (workload, k)
+            assert torch.equal(packs[k][1], exp[k][1]), (workload, k)
+    # (2) eager == graph, bit for bit
+    assert l_eager == l_graph
+    for key in ("params", "m", "v"):
+        assert torch.equal(s_eager[key], s_graph[key]), key
+    assert s_eager["counter"] == s_graph["counter"] == N_STEPS
+    # (3) the fp32 kernels on the same batches
+    l32, xs32, s32 = _run_fp32(lib, cuda_dev, wl, N_STEPS)
+    for k in range(3):
+        assert torch.equal(xs32[k], exp[k][2]), k           # same Philox stream on the fp32 side
+    for k in range(N_STEPS):
+        assert abs(l_eager[k] - l32[k]) <= 2e-2 * abs(l32[k]), (k, l_eager[k], l32[k])
+    P = s_eager["P"]
+    p0 = bench.init_flat(F, H).to(cuda_dev)
+    _assert_params(s_eager["params"][:P], s32["params"][:P], p0, N_STEPS, bench.LR, F, H)

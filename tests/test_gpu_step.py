@@ -405,6 +405,114 @@ def test_train_py_stdout_matches_reference(golden, tmp_path, extra):
     assert os.path.exists(tmp_path / "ck" / "epoch5" / "latest")
 
 
+def _engine_on_reference_model(cfg_extra=None, seed=42):
+    import b200ds
+    torch.manual_seed(seed)
+    net = torch.nn.Sequential(torch.nn.Linear(20, 64), torch.nn.ReLU(), torch.nn.Linear(64, 1))
+    p = {"w1": net[0].weight.detach().clone(), "b1": net[0].bias.detach().clone(),
+         "w2": net[2].weight.detach().clone(), "b2": net[2].bias.detach().clone()}
+    opt = torch.optim.Adam(net.parameters(), lr=1e-3)
+    cfg = {"train_batch_size": 64, "gradient_accumulation_steps": 1, "fp16": {"enabled": False}, "zero_optimization": {"stage": 0}}
+    cfg.update(cfg_extra or {})
+    engine, _, _, _ = b200ds.initialize(model=net, optimizer=opt, config=cfg)
+    return engine, net, opt, p
+
+
+def test_checkpoint_holds_the_trained_tensors_and_loads_back(cuda_dev, tmp_path):
+    """engine.save_checkpoint (train.py:123-125) after N steps: the .pt file's module.* tensors are the engine's
+    flat buffer and the oracle's parameters after the same N steps; load_checkpoint into a fresh engine, then
+    three more steps on both: parameters, Adam moments and losses stay bit-equal."""
+    import b200ds
+    x, y = ora.make_dataset(2000, 20, 42)
+    engine, net, opt, p = _engine_on_reference_model()
+    crit = b200ds.BCEWithLogitsLoss()
+    flat = ora.flatten(p)
+    st = ora.AdamState()
+
+    def steps(eng, lo, hi, track=False):
+        out = []
+        for s in range(lo, hi):
+            bi = torch.arange(s * 4, s * 4 + 4)
+            loss = crit(eng(x[bi].to(cuda_dev)), y[bi].to(cuda_dev))
+            eng.backward(loss)
+            eng.step()
+            out.append(loss.item())
+            if track:
+                pp = ora.unflatten(flat, 20, 64)
+                z, h = ora.forward(pp, x[bi])
+                ora.adam_update(flat, ora.flatten(ora.backward(pp, x[bi], y[bi], z, h)), st, 1e-3)
+        return out
+
+    steps(engine, 0, 7, track=True)
+    assert engine.save_checkpoint(str(tmp_path / "ck"), client_state={"epoch": 3})
+    tag = open(tmp_path / "ck" / "latest").read().strip()
+    assert tag == "global_step7"
+    state = torch.load(tmp_path / "ck" / tag / "mp_rank_00_model_states.pt", map_location="cpu", weights_only=False)
+    names = ["0.weight", "0.bias", "2.weight", "2.bias"]
+    assert sorted(state["module"]) == sorted(names)
+    saved = torch.cat([state["module"][n].reshape(-1) for n in names])
+    assert torch.equal(saved, engine.flat[: engine.P].cpu())                       # the file holds what the device holds
+    assert _rel(saved, flat) <= RTOL                                               # ... which is the oracle's state after 7 steps
+    assert state["global_steps"] == 7 and state["optimizer"]["step"] == 7 and state["client_state"] == {"epoch": 3}
+    assert float(opt.state_dict()["state"][0]["step"]) == 7.0                      # optimizer.state_dict() reports Adam's t
+    m_saved = torch.cat([state["optimizer"]["exp_avg"][n].reshape(-1) for n in names])
+    assert torch.equal(m_saved, engine.exp_avg[: engine.P].cpu())
+    # a fresh engine (different init) restored from the file continues bit for bit
+    engine2, net2, _, _ = _engine_on_reference_model(seed=7)
+    assert not torch.equal(engine2.flat, engine.flat)
+    path, client = engine2.load_checkpoint(str(tmp_path / "ck"))
+    assert path.endswith(tag) and client == {"epoch": 3} and engine2.global_steps == 7
+    assert torch.equal(engine2.flat, engine.flat) and torch.equal(engine2.exp_avg, engine.exp_avg)
+    assert torch.equal(net2[0].weight.detach(), net[0].weight.detach())            # module views follow
+    la, lb = steps(engine, 7, 10), steps(engine2, 7, 10)
+    assert la == lb
+    assert torch.equal(engine2.flat, engine.flat) and torch.equal(engine2.exp_avg_sq, engine.exp_avg_sq)
+    assert engine2.load_checkpoint(str(tmp_path / "nothing_here")) == (None, None)
+
+
+def test_engine_bf16_on_the_reference_model_runs_the_tensor_core_kernels(cuda_dev, golden):
+    """BASELINE config 3 semantics on the reference's own shapes (H = 64, batches of 4, ragged tail): bf16.enabled
+    pads the hidden layer and the batch up to the tensor-core shape class instead of silently running fp32.  The
+    first 200 reference steps (golden W = 1 losses, fp32) are tracked within north_star's bf16 tolerance 2e-2 on
+    the running mean, the padded hidden units stay exactly zero, and a ragged batch of 2 gives 2 logits."""
+    import b200ds
+    x, y = torch.from_numpy(golden["x"]), torch.from_numpy(golden["y"])
+    engine, net, opt, p = _engine_on_reference_model({"bf16": {"enabled": True}})
+    assert engine.H == 128 and engine.H_model == 64 and engine.P == 20 * 128 + 2 * 128 + 1
+    assert torch.equal(net[0].weight.detach().cpu(), torch.from_numpy(golden["init_w1"]))
+    crit = b200ds.BCEWithLogitsLoss()
+    g = torch.Generator(); g.manual_seed(1)            # any fixed order: compare against the fp32 oracle on the same batches
+    order = torch.randperm(2000, generator=g)
+    flat = ora.flatten(p)
+    st = ora.AdamState()
+    run16 = run32 = 0.0
+    for s in range(200):
+        bi = order[s * 4: s * 4 + (2 if s == 17 else 4)]
+        logits = engine(x[bi].to(cuda_dev))
+        assert engine._tc and logits.shape == (len(bi), 1)
+        loss = crit(logits, y[bi].to(cuda_dev))
+        engine.backward(loss)
+        engine.step()
+        pp = ora.unflatten(flat, 20, 64)
+        z, h = ora.forward(pp, x[bi])
+        want = float(ora.bce_with_logits(z, y[bi]))
+        ora.adam_update(flat, ora.flatten(ora.backward(pp, x[bi], y[bi], z, h)), st, 1e-3)
+        run16 += loss.item(); run32 += want
+        assert abs(loss.item() - want) <= 2e-2 * abs(want) + 2e-3, (s, loss.item(), want)
+    assert abs(run16 - run32) <= 2e-2 * run32
+    F, H, Hm = 20, engine.H, 64
+    fl = engine.flat.cpu()
+    assert float(fl[Hm * F: H * F].abs().max()) == 0.0 and float(fl[H * F + Hm: H * F + H].abs().max()) == 0.0
+    assert float(fl[H * F + H + Hm: H * F + 2 * H].abs().max()) == 0.0            # padded W1 rows, b1, W2: still zero
+    got = torch.cat([t.detach().reshape(-1).cpu() for t in (net[0].weight, net[0].bias, net[2].weight, net[2].bias)])
+    move = float((flat - ora.flatten(p)).norm())
+    assert float((got - flat).norm()) <= 2e-2 * float(flat.norm()), (float((got - flat).norm()), move)   # the parameters, within 2e-2
+    assert float((got - flat).abs().max()) <= 0.1 * 200 * 1e-3                    # and no element off by more than a tenth of Adam's reach
+    with pytest.raises(NotImplementedError):           # F + 2 > 32: no tensor-core path, and no silent fp32 substitute
+        wide = torch.nn.Sequential(torch.nn.Linear(40, 64), torch.nn.ReLU(), torch.nn.Linear(64, 1))
+        b200ds.initialize(model=wide, optimizer=torch.optim.Adam(wide.parameters()), config={"bf16": {"enabled": True}})
+
+
 def test_counted_philox_replays_consecutive_draws(lib, cuda_dev):
     """b200ds_philox_normal_counted with draw counter k == the (k+1)-th consecutive
     torch.randn(n) of a generator seeded the same way (what a CUDA-graph replay relies on)."""

@@ -20,7 +20,8 @@ sc = torch.zeros(lib.b200ds_mlp_backward_tc_scratch_bytes(B, F, H), dtype=torch.
 st = torch.cuda.current_stream().cuda_stream
 _lib.check(lib.b200ds_pack_x_bf16(x.data_ptr(), B, F, xq.data_ptr(), st))
 _lib.check(lib.b200ds_pack_params_bf16(params.data_ptr(), F, H, wq.data_ptr(), st))
-def fwd(): _lib.check(lib.b200ds_mlp_forward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), B, F, H, z.data_ptr(), st))
+fsc = torch.zeros(max(256, lib.b200ds_mlp_forward_tc_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
+def fwd(): _lib.check(lib.b200ds_mlp_forward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), B, F, H, z.data_ptr(), fsc.data_ptr(), fsc.numel(), st))
 def bwd(): _lib.check(lib.b200ds_mlp_backward_tc(xq.data_ptr(), wq.data_ptr(), params.data_ptr(), dz.data_ptr(), B, F, H, g.data_ptr(), sc.data_ptr(), sc.numel(), st))
 yl = (torch.rand(B, device=dev) > 0.5).float()
 ls = torch.zeros(1, device=dev)

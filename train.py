@@ -22,6 +22,8 @@ batches come from the device-resident copy of the dataset instead of DataLoader 
 Extension flags (all default off, the reference ignores unknown flags the same way):
   --fused-steps   run each epoch through the fused multi-step kernel (identical numbers)
   --no-checkpoint skip the per-epoch checkpoint
+  --bf16          ds_config["bf16"] = {"enabled": True}: the tcgen05 kernels on bf16 operands (BASELINE config 3)
+  --zero-stage N  ds_config["zero_optimization"]["stage"] = N (0 or 1; BASELINE config 5)
 """
 import argparse
 import os
@@ -50,6 +52,8 @@ def cli(argv=None):
     ap.add_argument("--save-dir", type=str, default="ds_checkpoints")
     ap.add_argument("--fused-steps", action="store_true")
     ap.add_argument("--no-checkpoint", action="store_true")
+    ap.add_argument("--bf16", action="store_true")
+    ap.add_argument("--zero-stage", type=int, default=0)
     known, _unknown = ap.parse_known_args(argv)
     return known
 
@@ -93,6 +97,10 @@ def run(opts):
         "fp16": {"enabled": False},
         "zero_optimization": {"stage": 0},
     }
+    if opts.bf16:                  # BASELINE config 3: bf16 operands on the tensor cores (fp32 master weights)
+        ds_config["bf16"] = {"enabled": True}
+    if opts.zero_stage:            # BASELINE config 5: ZeRO-1-style sharded optimizer step
+        ds_config["zero_optimization"] = {"stage": opts.zero_stage}
     optimizer = torch.optim.Adam(model.parameters(), lr=opts.lr)
     engine, optimizer, _, _ = deepspeed.initialize(args=ds_config, model=model, optimizer=optimizer,
                                                    model_parameters=model.parameters(), config=ds_config)
