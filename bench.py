@@ -46,6 +46,9 @@ def parse():
     ap.add_argument("--precision", default="auto", choices=["auto", "fp32", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-tiny", action="store_true")
+    ap.add_argument("--ref-rank", type=int, default=-1)        # internal: a gloo worker of the multi-process CPU reference
+    ap.add_argument("--ref-port", type=int, default=29611)
+    ap.add_argument("--ref-threads", type=int, default=0)
     return ap.parse_known_args()[0]
 
 
@@ -138,28 +141,51 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------ reference arm (CPU)
-def cpu_reference_run(wl, steps, warmup, budget_s=None):
+def workload_config(name, wl, world):
+    """The part of `config` both arms print identically (the driver compares the two lines)."""
+    return {"workload": f"{name}: train.py step (train.py:104-117), F={wl['F']} H={wl['H']}, {wl['B']} samples per rank per step "
+                        f"drawn from N(0,1) every step with the label rule of train.py:22-23, Adam, {world} rank(s)",
+            "per_gpu_batch": wl["B"], "n_features": wl["F"], "hidden": wl["H"], "parallelism": f"dp{world}"}
+
+
+def cpu_reference_run(wl, steps, warmup, budget_s=None, threads=None, rank=0, world=1):
     """The reference's own CPU path for this step (torch nn.Sequential + BCEWithLogitsLoss
-    + autograd + optim.Adam, as train.py:26-36,85,96,107-114 use them; DeepSpeed stage 0 at
-    world 1 adds nothing) via the oracle's torch-native restatement, on all host cores.
-    Each step works on a bounded sample of the per-GPU batch."""
+    + autograd + optim.Adam, as train.py:26-36,85,96,107-114 use them) via the oracle's torch-native
+    restatement, on FULL per-rank batches (wl["B"] samples per step, as the GPU arm).  world > 1: this is one of
+    `world` gloo processes; gradients are summed over the ranks, then scaled by 1/world (DeepSpeed stage 0,
+    train.py:113), through one flat bucket."""
     from oracle import reference_step as ora
     cores = len(os.sched_getaffinity(0))
-    torch.set_num_threads(cores)
+    threads = threads or cores
+    torch.set_num_threads(threads)
     B, F, H = wl["B"], wl["F"], wl["H"]
-    Bs = min(B, 8192)
     torch.manual_seed(SEED)
     p = ora.init_params(F, H)
     state = {}
+    torch.manual_seed(SEED + 1000003 * rank)        # a different batch stream per rank, as on the GPU arm
+    avg = None
+    if world > 1:
+        import torch.distributed as dist
+
+        def avg(grads):
+            flat = torch.cat([g.reshape(-1) for g in grads])
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+            flat.mul_(1.0 / world)
+            o = 0
+            for g in grads:
+                g.copy_(flat[o:o + g.numel()].view_as(g)); o += g.numel()
 
     def one():
-        x = torch.randn(Bs, F)
+        x = torch.randn(B, F)
         y = ora.label_rule(x)
-        loss, _ = ora.torch_native_step(p, x, y, state, LR)
+        loss, _ = ora.torch_native_step(p, x, y, state, LR, average_grads=avg)
         return float(loss)
 
     for _ in range(max(1, warmup)):
         one()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
     t0 = time.perf_counter()
     done = 0
     for _ in range(steps):
@@ -167,11 +193,29 @@ def cpu_reference_run(wl, steps, warmup, budget_s=None):
         done += 1
         if budget_s is not None and time.perf_counter() - t0 > budget_s:
             break
+    if world > 1:
+        dist.barrier()
     dt = time.perf_counter() - t0
-    return dict(value=Bs * done / dt, unit="samples/s", cores=cores, kind="port",
-                sample=f"{done} steps x {Bs} of the {B}-sample batch (F={F}, H={H}), torch {torch.__version__} CPU fp32, "
-                       f"{cores} threads, batch drawn with torch.randn on the host each step",
-                ms_per_step=1e3 * dt / done, steps=done, Bs=Bs)
+    return dict(value=world * B * done / dt, unit="samples/s", cores=threads * world, kind="port",
+                sample=f"{done} full steps of {B} samples per rank (F={F}, H={H}), {world} process(es) x {threads} thread(s) of "
+                       f"{cores} host cores{', gloo all-reduce of the flat gradient bucket' if world > 1 else ''}, torch "
+                       f"{torch.__version__} CPU fp32, batch drawn with torch.randn on the host each step",
+                ms_per_step=1e3 * dt / done, steps=done, Bs=B, threads=threads)
+
+
+def reference_worker(a):
+    """One gloo rank of the multi-process CPU reference (spawned by rank 0 of `--impl reference` when --gpus > 1)."""
+    import torch.distributed as dist
+    rank, world = a.ref_rank, a.gpus
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{a.ref_port}", rank=rank, world_size=world)
+    r = cpu_reference_run(WORKLOADS[a.workload], a.steps, a.warmup, threads=a.ref_threads, rank=rank, world=world)
+    t = torch.tensor([r["ms_per_step"]], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        r["ms_per_step"] = float(t)
+        r["value"] = world * r["Bs"] * 1e3 / float(t)
+        print("REFWORKER " + json.dumps(r), flush=True)
+    dist.destroy_process_group()
 
 
 # ------------------------------------------------------------------------------ our arm
@@ -626,28 +670,57 @@ def bench_tiny(lib, ctx, dev, world, rank, a, barrier, brief=False):
 
 
 def run_reference(a):
+    """`--impl reference`: the reference's CPU implementation of the step on the box's host cores, same workload,
+    metric and unit as our arm, full-size steps.  N = 1: one process with every core.  N > 1:
+    N gloo processes, OMP threads = cores // N each, spawned by rank 0 (the other torchrun ranks exit at once)."""
+    import subprocess
     rank = int(os.environ.get("RANK", 0))
-    world = int(os.environ.get("WORLD_SIZE", 1))
     if rank != 0:
         return
+    world = max(1, a.gpus)
     wl = WORKLOADS[a.workload]
-    r = cpu_reference_run(wl, steps=a.steps, warmup=max(1, a.warmup))
+    cores = len(os.sched_getaffinity(0))
+    extra = {}
+    if world == 1:
+        r = cpu_reference_run(wl, steps=a.steps, warmup=max(1, a.warmup))
+    else:
+        threads = max(1, cores // world)
+        env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE", "MASTER_ADDR",
+                                                                  "MASTER_PORT", "TORCHELASTIC_RUN_ID", "GROUP_RANK", "ROLE_RANK")}
+        env["OMP_NUM_THREADS"] = str(threads)
+        port = 29611 + (os.getpid() % 2000)
+        procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--gpus", str(world),
+                                   "--steps", str(a.steps), "--warmup", str(max(1, a.warmup)), "--workload", a.workload,
+                                   "--ref-rank", str(i), "--ref-port", str(port), "--ref-threads", str(threads)],
+                                  env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True) for i in range(world)]
+        outs = [p.communicate(timeout=1500) for p in procs]
+        if any(p.returncode for p in procs):
+            raise RuntimeError("CPU reference worker failed: " + " | ".join(o[1][-400:] for o in outs))
+        r = json.loads([ln for ln in outs[0][0].splitlines() if ln.startswith("REFWORKER ")][-1][len("REFWORKER "):])
+    if a.workload != "tiny":
+        # the figure the reference itself pins (slurm_train.sbatch:16, OMP_NUM_THREADS=1): one thread, a bounded sample
+        one = cpu_reference_run(wl, steps=2, warmup=1, budget_s=20.0, threads=1)
+        extra["one_thread"] = {"value": one["value"], "unit": "samples/s", "cores": 1, "sample": one["sample"]}
+        torch.set_num_threads(cores)
+    cfg = workload_config(a.workload, wl, world)
+    cfg["arm"] = ("CPU reference path: %d process(es) x %d thread(s), gloo" % (world, r["threads"])) if world > 1 else \
+                 ("CPU reference path: one process, %d threads" % r["threads"])
     line = dict(impl="reference", metric="train_samples_per_sec", value=r["value"], unit="samples/s", n_gpus=world,
                 steps=r["steps"], warmup=max(1, a.warmup), ms_per_step=r["ms_per_step"], higher_is_better=True,
                 scaling="weak", vs_baseline=None, dtype="f32",
                 data="synthetic: host torch.randn batches with the label rule of train.py:22-23; nn.Linear default init",
-                config={"workload": f"{a.workload}: train.py step, F={wl['F']} H={wl['H']}, CPU reference path on "
-                                    f"{r['Bs']}-sample slices of the {wl['B']}-sample per-GPU batch",
-                        "per_gpu_batch": wl["B"], "n_features": wl["F"], "hidden": wl["H"], "parallelism": "cpu"},
+                config=cfg,
                 cpu_baseline={k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 e2e=dict(value=r["value"], unit="samples/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0),
-                gpu_launches=0)
+                gpu_launches=0, **extra)
     print(json.dumps(line), flush=True)
 
 
 if __name__ == "__main__":
     args = parse()
-    if args.impl == "reference":
+    if args.impl == "reference" and args.ref_rank >= 0:
+        reference_worker(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

@@ -294,10 +294,12 @@ def _bf16_step(p, bx, by):
 
 
 # --------------------------------------------------------------------------- torch-native cross-check
-def torch_native_step(p, bx, by, opt_state: dict, lr: float):
+def torch_native_step(p, bx, by, opt_state: dict, lr: float, average_grads=None):
     """One step using the SAME torch objects train.py uses (nn.Linear/ReLU/Sequential,
     nn.BCEWithLogitsLoss, autograd, torch.optim.Adam) -- used by the tests to pin the
-    written-out math above, and by bench.py --impl reference as the timed CPU path."""
+    written-out math above, and by bench.py --impl reference as the timed CPU path.
+    `average_grads(list_of_param_grads)`, when given, runs between backward and the optimizer step:
+    the stage-0 gradient averaging of engine.backward (train.py:113) for world > 1."""
     net = opt_state.get("net")
     if net is None:
         h, f = p["w1"].shape
@@ -313,5 +315,7 @@ def torch_native_step(p, bx, by, opt_state: dict, lr: float):
     loss = opt_state["crit"](logits, by)
     opt.zero_grad(set_to_none=True)
     loss.backward()
+    if average_grads is not None:
+        average_grads([q.grad for q in net.parameters()])
     opt.step()
     return loss.detach(), logits.detach()

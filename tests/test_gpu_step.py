@@ -408,6 +408,7 @@ def test_train_py_stdout_matches_reference(golden, tmp_path, extra):
 def _engine_on_reference_model(cfg_extra=None, seed=42):
     import b200ds
     torch.manual_seed(seed)
+    ora.make_dataset(2000, 20, seed)          # the reference draws the dataset before it builds the model (train.py:63,76)
     net = torch.nn.Sequential(torch.nn.Linear(20, 64), torch.nn.ReLU(), torch.nn.Linear(64, 1))
     p = {"w1": net[0].weight.detach().clone(), "b1": net[0].bias.detach().clone(),
          "w2": net[2].weight.detach().clone(), "b2": net[2].bias.detach().clone()}
