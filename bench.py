@@ -255,11 +255,9 @@ class WideStep:
         # W > 1: gradient exchange + Adam as one peer-memory kernel (NVLink loads of the peers' buckets,
         # fixed summation order); B200DS_BENCH_NCCL=1 selects ncclAllReduce + the Adam kernel instead
         self.p2p = world > 1 and not os.environ.get("B200DS_BENCH_NCCL")
-        # B200DS_BENCH_FUSED_UPDATE=1: finish + exchange + Adam + pack as ONE kernel (b200ds_update_tc).  Not the
-        # default: measured on one box, 200 steps, three runs each, it is 2 us per step slower at one rank (102.5 vs
-        # 100.35 us: its 64 CTAs pull the 9.4 MB of split partials more slowly than the 512 CTAs of the finish
-        # kernel) and equal at two ranks.
-        self.fused_update = self.tc and bool(os.environ.get("B200DS_BENCH_FUSED_UPDATE")) and (world == 1 or self.p2p)
+        # finish pass + gradient exchange + Adam + operand pack as b200ds_update_tc (one launch at one rank, two with
+        # several); B200DS_BENCH_SPLIT_UPDATE=1 selects the separate finish / exchange+Adam / pack kernels (A/B arm)
+        self.fused_update = self.tc and not os.environ.get("B200DS_BENCH_SPLIT_UPDATE") and (world == 1 or self.p2p)
         if self.p2p:
             # collective; if any rank cannot map its peers (no peer access on this box) every rank takes the NCCL exchange
             import torch.distributed as dist
@@ -279,7 +277,9 @@ class WideStep:
         """kernels of this library launched per step"""
         if not self.tc:
             return 7                      # philox, label, forward, loss, backward, finish, adam
-        return 4 if self.fused_update else 6   # gen_batch, forward, loss+backward, update | ... finish, adam, pack_w1
+        if self.fused_update:
+            return 4 if self.world == 1 else 5     # gen_batch, forward, loss+backward, update (publish + collect for W > 1)
+        return 6                                   # ... finish, adam (or exchange+adam), pack_w1
 
     def step(self, st, ev_pair=None):
         lib, chk = self.lib, self._lib.check

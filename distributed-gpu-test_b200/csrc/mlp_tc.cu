@@ -66,77 +66,136 @@ pack_x_kernel(const float* __restrict__ x, int64_t rows, int64_t batch, int F, u
   xq[t] = *reinterpret_cast<uint4*>(v);
 }
 
-// Generated batch straight into the tensor-core pack (BASELINE config 4: the batch is drawn on
-// the device every step).  Element (row, k) is element li = row*F + k of
-// torch.randn(B*F, device='cuda') under (seed, offset): Philox counter offset/4 + li/(4*nthreads),
-// subsequence li % nthreads, output (li / nthreads) % 4 -- the mapping of philox_normal_kernel.
-// Four threads per row.  Each draws ceil(F/4) of the row's values (an even split: one Philox
-// evaluation + Box-Muller per value is the whole cost of the kernel), the row is assembled in
-// shared memory, and each thread then writes one 16-byte chunk of xq (same thread->address
-// map as pack_x_kernel); thread 0 of the row evaluates the label rule (train.py:22-23) on the
-// fp32 values in the order label_rule_kernel uses.  fp32 x is never written to global memory.
-template <typename idx_t, int PER>      // idx_t: uint32_t when batch*F < 2^31 (64-bit div/mod would dominate the kernel);
-__global__ void __launch_bounds__(256)  // PER = ceil(F/4) values per thread, a compile-time count so that the PER
-gen_batch_kernel(uint4* __restrict__ xq, float* __restrict__ y, int64_t batch, int F, uint2 key, uint64_t ctr0,
-                 int64_t nthreads, uint32_t inv_nthreads /* floor(2^32 / nthreads) */, int calls,
-                 const unsigned long long* __restrict__ draw_counter) {
-  __shared__ float xs[64][33];                                           // the block's 64 rows, fp32
-  if (draw_counter) ctr0 += (uint64_t)(*draw_counter) * (uint64_t)calls;
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;      // batch % 8 == 0: whole warps only
-  const int r8 = (int)(t & 7), c = (int)((t >> 3) & 3);
-  const int64_t row = ((t >> 5) << 3) + r8;
-  if (row >= batch) return;                                              // whole warps (batch % 8 == 0)
-  float* xr = xs[(threadIdx.x >> 5) * 8 + r8];
-  // independent Philox chains of a thread are unrolled side by side (one chain alone is latency-bound)
-  constexpr int per = PER;
-  float val[PER];
-#pragma unroll
-  for (int j = 0; j < PER; ++j) {                                        // branch-free: a slot past F redraws column F-1 and is dropped
-    const int k = min(c * per + j, F - 1);
-    const idx_t li = (idx_t)row * (idx_t)F + (idx_t)k;
-    idx_t tt, sub;
-    if (sizeof(idx_t) == 4) {                                            // li / nthreads by multiply-high and one correction
-      uint32_t qd = __umulhi((uint32_t)li, inv_nthreads);
-      uint32_t rm = (uint32_t)li - qd * (uint32_t)nthreads;
-      const bool fix = rm >= (uint32_t)nthreads;
-      qd += fix ? 1u : 0u;
-      rm -= fix ? (uint32_t)nthreads : 0u;
-      tt = (idx_t)qd; sub = (idx_t)rm;
-    } else {
-      tt = li / (idx_t)nthreads;
-      sub = li - tt * (idx_t)nthreads;
-    }
-    const uint64_t ctr = ctr0 + (uint64_t)(tt >> 2);
-    const uint4 r = philox4x32_10(make_uint4((unsigned)ctr, (unsigned)(ctr >> 32), (unsigned)sub, (unsigned)((uint64_t)sub >> 32)), key);
-    const float2 p = box_muller((tt & 2) ? r.z : r.x, (tt & 2) ? r.w : r.y);
-    val[j] = normal_transform((tt & 1) ? p.y : p.x);
-  }
-#pragma unroll
-  for (int j = 0; j < PER; ++j) {
-    const int k = c * per + j;
-    if (k < F) xr[k] = val[j];
-  }
-  __syncwarp();                                                          // the 4 threads of a row share a warp
-  __nv_bfloat16 q[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int k = c * 8 + j;
-    q[j] = __float2bfloat16(k < F ? xr[k] : (k < F + 2 ? 1.f : 0.f));
-  }
-  xq[t] = *reinterpret_cast<uint4*>(q);
-  if (c == 0) {      // label: sum of columns 0 .. F/2-1 in index order
-    float acc = 0.f;
-    const int half = F >> 1;
-    for (int k = 0; k < half; ++k) acc += xr[k];
-    y[row] = acc > 0.f ? 1.f : 0.f;
+// Generated batch straight into the tensor-core pack (BASELINE config 4: the batch is drawn on the device every
+// step).  Element (row, k) is element li = row*F + k of torch.randn(B*F, device='cuda') under (seed, offset): Philox
+// counter offset/4 + j/4, subsequence sub, output j % 4, where li = sub + nthreads * j -- the mapping of
+// philox_normal_kernel, i.e. of ATen's distribution kernels.  The kernel uses torch's own thread geometry: thread `sub`
+// evaluates Philox4x32-10 once per call index c and uses ALL FOUR outputs -- the elements sub + nthreads*(4c + i),
+// i = 0..3, four places of the batch ~nthreads/F rows apart -- converts each to bf16 and stores it at its place in the
+// tiled pack.  (The first version gave every ELEMENT a thread and a Philox evaluation of its own, keeping one output of
+// four: 3.3 times the generator work for the benchmark shape.)
+// A row's 64-byte pack and its label (train.py:22-23: sum of columns 0 .. F/2-1 in index order, > 0) need the row's F
+// neighbouring elements: the block keeps its fp32 values in shared memory, 256 consecutive elements per (c, i), plus a
+// halo of F - 1 elements past the end that a few threads draw in addition (one more evaluation per call index serves
+// all four i).  A row belongs to the block that holds its column 0: that block writes the whole row -- one 16-byte
+// store per k chunk, the thread -> address pattern of pack_x_kernel -- and its label.  fp32 x never reaches global
+// memory, and nothing is stored in pieces smaller than 16 bytes.
+constexpr int kGenMaxCalls = 4;            // Philox calls per thread kept in flight (more calls -> outer loop)
+constexpr int kGenHaloMax = 32;            // F - 1 <= 29
+
+template <typename idx_t>
+__device__ __forceinline__ void gen_divmod(idx_t li, uint32_t d, uint32_t inv, idx_t* q, uint32_t* r) {
+  if (sizeof(idx_t) == 4) {                // li / d by multiply-high and one correction (64-bit div/mod would dominate)
+    uint32_t qd = __umulhi((uint32_t)li, inv);
+    uint32_t rm = (uint32_t)li - qd * d;
+    const bool fix = rm >= d;
+    qd += fix ? 1u : 0u;
+    rm -= fix ? d : 0u;
+    *q = (idx_t)qd; *r = rm;
+  } else {
+    *q = li / (idx_t)d;
+    *r = (uint32_t)(li - *q * (idx_t)d);
   }
 }
 
-constexpr int kPackRows = 64;             // rows of W1 per pack_w1 block (256 threads = 64 rows x 4 k chunks)
+__device__ __forceinline__ void gen_normals4(uint64_t ctr, uint64_t sub, uint2 key, float (&out)[4]) {
+  const uint4 r = philox4x32_10(make_uint4((unsigned)ctr, (unsigned)(ctr >> 32), (unsigned)sub, (unsigned)(sub >> 32)), key);
+  const float2 p = box_muller(r.x, r.y), q = box_muller(r.z, r.w);
+  out[0] = normal_transform(p.x); out[1] = normal_transform(p.y);
+  out[2] = normal_transform(q.x); out[3] = normal_transform(q.y);
+}
+
+template <typename idx_t>
+__global__ void __launch_bounds__(256, 8)      // torch's geometry is 8 blocks of 256 per SM: all of them resident (one wave) needs <= 32 registers
+gen_batch_kernel(unsigned char* __restrict__ xq, float* __restrict__ y, int64_t batch, int F, uint2 key, uint64_t ctr0,
+                 uint32_t nthreads, int calls, uint32_t inv_F /* floor(2^32 / F) */, uint32_t inv_nthreads,
+                 const unsigned long long* __restrict__ draw_counter) {
+  __shared__ float xs[kGenMaxCalls * 4][256 + kGenHaloMax];
+  if (draw_counter) ctr0 += (uint64_t)(*draw_counter) * (uint64_t)calls;
+  const int t = threadIdx.x;
+  const uint32_t sub = blockIdx.x * 256u + t;
+  const idx_t n = (idx_t)batch * (idx_t)F;
+  const int half = F >> 1, halo = F - 1;
+  for (int c0 = 0; c0 < calls; c0 += kGenMaxCalls) {
+    const int nc = min(kGenMaxCalls, calls - c0);
+    // ---- this thread's elements: up to kGenMaxCalls independent Philox chains side by side
+    float val[kGenMaxCalls][4];
+#pragma unroll
+    for (int cc = 0; cc < kGenMaxCalls; ++cc) {
+      if (cc < nc && (idx_t)sub + (idx_t)nthreads * (idx_t)(4 * (c0 + cc)) < n)       // any of the four inside the batch
+        gen_normals4(ctr0 + (uint64_t)(c0 + cc), sub, key, val[cc]);
+      else
+        val[cc][0] = val[cc][1] = val[cc][2] = val[cc][3] = 0.f;
+    }
+#pragma unroll
+    for (int cc = 0; cc < kGenMaxCalls; ++cc) {
+      if (cc >= nc) continue;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) xs[cc * 4 + i][t] = val[cc][i];
+    }
+    // ---- halo: the `halo` elements after the block's 256, per (c, i)
+    if (t < halo) {
+      const uint32_t sub_h = blockIdx.x * 256u + 256u + t;
+      if (sub_h < nthreads) {              // same call index, next subsequences: one evaluation serves i = 0..3
+        for (int cc = 0; cc < nc; ++cc) {
+          float hv[4] = {0.f, 0.f, 0.f, 0.f};
+          if ((idx_t)sub_h + (idx_t)nthreads * (idx_t)(4 * (c0 + cc)) < n) gen_normals4(ctr0 + (uint64_t)(c0 + cc), sub_h, key, hv);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) xs[cc * 4 + i][256 + t] = hv[i];
+        }
+      } else {                             // last block: the element after (nthreads - 1, j) is (0, j + 1)
+        for (int cc = 0; cc < nc; ++cc)
+          for (int i = 0; i < 4; ++i) {
+            const idx_t li = (idx_t)sub_h + (idx_t)nthreads * (idx_t)(4 * (c0 + cc) + i);
+            float v1 = 0.f;
+            if (li < n) {
+              idx_t j; uint32_t sb;
+              gen_divmod<idx_t>(li, nthreads, inv_nthreads, &j, &sb);
+              float hv[4];
+              gen_normals4(ctr0 + (uint64_t)(j >> 2), sb, key, hv);
+              v1 = hv[(int)(j & 3)];
+            }
+            xs[cc * 4 + i][256 + t] = v1;
+          }
+      }
+    }
+    __syncthreads();
+    // ---- rows whose column 0 lies among this block's 256 elements of some (c, i): at most 256 / F + 1 per (c, i);
+    // a work item is (combo, row-in-combo, k chunk)
+    const int rows_per = 256 / F + 1;
+    for (int w = t; w < nc * 4 * rows_per * (KP / 8); w += 256) {
+      const int c8 = w & (KP / 8 - 1), wr = w >> 2;                    // KP / 8 == 4
+      const int combo = wr / rows_per, ri = wr - combo * rows_per;
+      const idx_t base = (idx_t)blockIdx.x * 256 + (idx_t)nthreads * (idx_t)(4 * c0 + combo);
+      if (base >= n) continue;
+      idx_t row0; uint32_t k0;
+      gen_divmod<idx_t>(base, (uint32_t)F, inv_F, &row0, &k0);
+      const idx_t row = row0 + (k0 ? 1 : 0) + (idx_t)ri;              // first row starting at or after `base`, then the next ones
+      const idx_t start = row * (idx_t)F;                             // li of its column 0
+      if (start >= base + 256 || row >= (idx_t)batch) continue;
+      const float* xr = &xs[combo][(int)(start - base)];
+      __nv_bfloat16 q[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int k = c8 * 8 + j;
+        q[j] = __float2bfloat16(k < F ? xr[k] : (k < F + 2 ? 1.f : 0.f));
+      }
+      *reinterpret_cast<uint4*>(xq + tiled_byte((int64_t)row, c8 * 8)) = *reinterpret_cast<uint4*>(q);
+      if (c8 == 0) {                                                   // label: sum of columns 0 .. F/2-1 in index order
+        float acc = 0.f;
+        for (int k = 0; k < half; ++k) acc += xr[k];
+        y[row] = acc > 0.f ? 1.f : 0.f;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+constexpr int kPackRows = 16;             // rows of W1 per block of the pack (pack_w1_kernel: 16 rows x 4 k chunks; the update kernel: 16 warps)
 
 // Also emits, per block of 64 rows, vpart[block][k] = sum_{n in block} w2[n] * w1q[n,k]: the forward
 // sums the blocks of its slice in a fixed order to get v = w1q^T w2 (the linear half of relu).
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(4 * kPackRows)
 pack_w1_kernel(const float* __restrict__ params, Layout L, uint4* __restrict__ w1q, float* __restrict__ vpart) {
   __shared__ float prod[kPackRows][33];
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;     // H % 64 == 0: no partial blocks
@@ -768,113 +827,89 @@ mlp_bwd_tc_finish(const float* __restrict__ partial, const float* __restrict__ d
 }
 
 // ------------------------------------------------------------------ finish + exchange + Adam + operand pack
-// Everything between the backward kernel and the next forward as ONE launch: the split partials of
-// S are summed (mlp_bwd_tc_finish), the gradients of the W ranks are exchanged through peer memory
-// and summed in rank order (p2p.cu; skipped for one rank), Adam is applied (adam.cu) and the new
-// W1 / b1 are packed to bf16 with the partials of v = w1q^T w2 (pack_w1_kernel).  Thread layout of
-// pack_w1_kernel: a block owns 64 hidden units, four threads per unit, eight k each; the thread
-// that owns slot k owns the parameter behind it (W1[n,k] for k < F, b1[n] at k = F, W2[n] at
-// k = F + 1; b2 belongs to thread 0 of block 0).  For one rank the result is bit-identical to the
-// three kernels it replaces.  Exchange buffer layout: [n][32] slots, then db2.
-template <bool kCounted>
-__global__ void __launch_bounds__(256)
+// Everything between the backward kernel and the next forward: the split partials of S are summed
+// (mlp_bwd_tc_finish), the gradients of the W ranks are exchanged through peer memory and summed in rank order
+// (skipped for one rank), Adam is applied (adam.cu) and the new W1 / b1 are packed to bf16 with the partials of
+// v = w1q^T w2 (pack_w1_kernel).  One warp per hidden unit n, lane = k, the mapping of mlp_bwd_tc_finish: lane k < F
+// owns W1[n,k], lane F owns b1[n], lane F + 1 owns W2[n]; b2 belongs to lane 31 of the first warp of CTA 0.  A CTA is
+// kPackRows units, H / kPackRows CTAs.  For one rank the result is bit-identical to the three kernels it replaces.
+//   kPhase 0  one rank: all of it in one launch;
+//   kPhase 1  several ranks, first launch: finish pass, then the gradients are PUSHED: every rank stores its own into
+//             slot `rank` of every rank's exchange buffer (its own included), layout [unit][32] + db2, then -- last CTA
+//             of the grid -- the epoch into its flag at every peer;
+//   kPhase 2  second launch: wait for every rank's flag (they sit in local memory), add the W slots up in rank order
+//             (local reads only: the data crossed NVLink one way, once), Adam, pack.
+// Two launches because a CTA of phase 2 waits for OTHER GPUs only, never for a CTA of its own grid: no CTA has to be
+// resident for another one to make progress, so the grid can be as large as the work wants.
+template <bool kCounted, int kPhase>
+__global__ void __launch_bounds__(32 * kPackRows)
 mlp_update_tc_kernel(const float* __restrict__ partial, const float* __restrict__ db2_part, const float* __restrict__ loss_part,
                      int n_splits, double inv_batch, float* __restrict__ params, float* __restrict__ grads,
-                     float* __restrict__ m, float* __restrict__ v, Layout L, uint4* __restrict__ w1q, float* __restrict__ vpart,
+                     float* __restrict__ m, float* __restrict__ v, Layout L, unsigned char* __restrict__ w1q, float* __restrict__ vpart,
                      AdamScalars s, double lr, double beta1, double beta2, int64_t step,
                      const unsigned long long* __restrict__ step_counter, float* __restrict__ loss_out, P2PDev d) {
   __shared__ float prod[kPackRows][33];
   __shared__ float sh[2];
   __shared__ bool last;
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;     // H % 64 == 0: no partial blocks
-  const int lane = threadIdx.x & 31;
-  const int r8 = (int)(t & 7), c = (int)((t >> 3) & 3);
-  const int n = (int)(((t >> 5) << 3) + r8);
-  const int rl = n - blockIdx.x * kPackRows;
-  const bool boss = blockIdx.x == 0 && threadIdx.x == 0;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int n = blockIdx.x * kPackRows + wib;                          // H % kPackRows == 0: no partial blocks
   const int F = L.F;
-  // ---- split partials of S[n, 8c .. 8c+7], summed in split order
-  float S[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) S[j] = 0.f;
-  {
-    const float4* p = reinterpret_cast<const float4*>(partial + (size_t)n * 32 + 8 * c);
-    const size_t stride4 = (size_t)L.H * 8;
-    int sp = 0;
-    for (; sp + 9 <= n_splits; sp += 9) {                // 18 loads in flight: the pass is latency-bound (64 CTAs)
-      float4 a[9], b[9];
-#pragma unroll
-      for (int u = 0; u < 9; ++u) { a[u] = __ldcg(p + (size_t)(sp + u) * stride4); b[u] = __ldcg(p + (size_t)(sp + u) * stride4 + 1); }
-#pragma unroll
-      for (int u = 0; u < 9; ++u) {
-        S[0] += a[u].x; S[1] += a[u].y; S[2] += a[u].z; S[3] += a[u].w;
-        S[4] += b[u].x; S[5] += b[u].y; S[6] += b[u].z; S[7] += b[u].w;
-      }
-    }
-    for (; sp < n_splits; ++sp) {
-      const float4 a = __ldcg(p + (size_t)sp * stride4), b = __ldcg(p + (size_t)sp * stride4 + 1);
-      S[0] += a.x; S[1] += a.y; S[2] += a.z; S[3] += a.w;
-      S[4] += b.x; S[5] += b.y; S[6] += b.z; S[7] += b.w;
-    }
-  }
-  if (threadIdx.x == 0) {                                // the optimizer's scalars
+  const bool boss = blockIdx.x == 0 && threadIdx.x == 31;              // looks after b2 (besides its own lane's parameter, if it has one)
+  const int64_t xi = (int64_t)n * 32 + lane, xb2 = (int64_t)L.H * 32;  // this thread's place in an exchange slot
+  float g = 0.f, gb2 = 0.f;
+  if (kPhase != 1 && threadIdx.x == 0) {                               // the optimizer's scalars
     double tt = kCounted ? (double)(*step_counter) : (double)step;
     double bc1 = 1.0 - pow(beta1, tt);
     double bc2 = 1.0 - pow(beta2, tt);
     sh[0] = (float)(-(lr / bc1));
     sh[1] = (float)sqrt(bc2);
   }
-  // ---- local gradients of this thread's slots
-  float w2 = params[L.off_w2() + n];
-  float b1 = params[L.off_b1() + n];
-  const float b1hi = __bfloat162float(__float2bfloat16(b1));
-  float pw[8];                                           // the parameter behind each slot
-  float g[8], tk[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int k = 8 * c + j;
-    float wq = 0.f;
-    pw[j] = 0.f;
-    if (k < F) {
-      pw[j] = params[L.off_w1() + (int64_t)n * F + k];
-      wq = __bfloat162float(__float2bfloat16(pw[j]));
-    } else if (k == F) {
-      pw[j] = b1;
-      wq = b1hi;
-    } else if (k == F + 1) {
-      pw[j] = w2;
-      wq = __bfloat162float(__float2bfloat16(b1 - b1hi));
+  if (kPhase != 2) {
+    // ---- the finish pass: split partials of S[n, lane] summed in split order, gradients from S
+    const float* p = partial + (size_t)n * 32 + lane;
+    const size_t stride = (size_t)L.H * 32;
+    float sacc = 0.f;
+    int sp = 0;
+    for (; sp + 8 <= n_splits; sp += 8) {           // 8 independent loads in flight, summed in order
+      float v0 = __ldcg(p + (size_t)(sp + 0) * stride), v1 = __ldcg(p + (size_t)(sp + 1) * stride), v2 = __ldcg(p + (size_t)(sp + 2) * stride),
+            v3 = __ldcg(p + (size_t)(sp + 3) * stride), v4 = __ldcg(p + (size_t)(sp + 4) * stride), v5 = __ldcg(p + (size_t)(sp + 5) * stride),
+            v6 = __ldcg(p + (size_t)(sp + 6) * stride), v7 = __ldcg(p + (size_t)(sp + 7) * stride);
+      sacc = ((((((((sacc + v0) + v1) + v2) + v3) + v4) + v5) + v6) + v7);
     }
-    g[j] = k <= F ? w2 * S[j] : 0.f;
-    tk[j] = wq * S[j];
+    for (; sp < n_splits; ++sp) sacc += __ldcg(p + (size_t)sp * stride);
+    const float w2 = params[L.off_w2() + n];
+    float wq = 0.f;
+    if (lane < F) {
+      wq = __bfloat162float(__float2bfloat16(params[L.off_w1() + (int64_t)n * F + lane]));
+      g = w2 * sacc;
+    } else if (lane == F || lane == F + 1) {
+      const float b1 = params[L.off_b1() + n];
+      const float hi = __bfloat162float(__float2bfloat16(b1));
+      wq = lane == F ? hi : __bfloat162float(__float2bfloat16(b1 - hi));
+      if (lane == F) g = w2 * sacc;
+    }
+    const float d2 = warp_sum(wq * sacc);
+    if (lane == F + 1) g = d2;
+    if (boss) {
+      for (int q = 0; q < n_splits; ++q) gb2 += db2_part[q];
+      if (loss_part) {           // fused loss: mean over the batch, split partials summed in split order in double
+        double ls = 0.0;
+        for (int q = 0; q < n_splits; ++q) ls += (double)loss_part[q];
+        *loss_out = (float)(ls * inv_batch);
+      }
+    }
   }
-  // dW2[n] = sum_k w1q[n,k] S[n,k]: the butterfly a 32-lane warp_sum over lane = k makes (k xor 16, 8 across the
-  // row's four threads, k xor 4, 2, 1 inside the thread)
-#pragma unroll
-  for (int j = 0; j < 8; ++j) tk[j] += __shfl_xor_sync(0xffffffffu, tk[j], 16);
-#pragma unroll
-  for (int j = 0; j < 8; ++j) tk[j] += __shfl_xor_sync(0xffffffffu, tk[j], 8);
-  {
-    const float a0 = tk[0] + tk[4], a1 = tk[1] + tk[5], a2 = tk[2] + tk[6], a3 = tk[3] + tk[7];
-    const float c0 = a0 + a2, c1 = a1 + a3;
-    const float d2 = c0 + c1;
-#pragma unroll
-    for (int j = 0; j < 8; ++j)
-      if (8 * c + j == F + 1) g[j] = d2;
-  }
-  float gb2 = 0.f;
-  if (boss) for (int sp = 0; sp < n_splits; ++sp) gb2 += db2_part[sp];
-  // ---- exchange over peer memory (p2p.cu's protocol), rank-order sum
-  if (d.world > 1) {
+  if (kPhase == 1) {
+    // ---- publish: slot `rank` of every rank's buffer, then (last CTA) the epoch into every peer's flag row
     const unsigned long long e = *d.epoch + 1;
-    const int64_t half = (int64_t)(e & 1) * d.cap;
-    float4* mine = reinterpret_cast<float4*>(d.xchg[d.rank] + half + (size_t)n * 32 + 8 * c);
-    mine[0] = make_float4(g[0], g[1], g[2], g[3]);
-    mine[1] = make_float4(g[4], g[5], g[6], g[7]);
-    if (boss) d.xchg[d.rank][half + (size_t)L.H * 32] = gb2;
+    const int64_t half = (int64_t)(e & 1) * d.world * d.cap + (int64_t)d.rank * d.cap;
+    for (int w = 0; w < d.world; ++w) {
+      d.push[w][half + xi] = g;
+      if (boss) d.push[w][half + xb2] = gb2;
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
-      __threadfence();                                   // device scope; the last CTA's system fence is cumulative
+      __threadfence_system();                            // this CTA's stores (ordered before by the barrier) are out
       last = atomicAdd(&d.tickets[0], 1u) == gridDim.x - 1;
     }
     __syncthreads();
@@ -883,27 +918,22 @@ mlp_update_tc_kernel(const float* __restrict__ partial, const float* __restrict_
       st_release_sys(&d.flags[threadIdx.x][d.rank], e);
       if (threadIdx.x == 0) d.tickets[0] = 0u;
     }
+    return;
+  }
+  if (kPhase == 2) {
+    const unsigned long long e = *d.epoch + 1;
     if (threadIdx.x < d.world) p2p_wait_flag(&d.flags[d.rank][threadIdx.x], e, (int)threadIdx.x, d);
     __syncthreads();
-    float4 lo4 = make_float4(0.f, 0.f, 0.f, 0.f), hi4 = lo4;
-    float sb2 = 0.f;
-    for (int w = 0; w < d.world; ++w) {
-      const float* base = d.xchg[w] + half;
-      const float4 a = ld_peer(reinterpret_cast<const float4*>(base + (size_t)n * 32 + 8 * c));
-      const float4 b = ld_peer(reinterpret_cast<const float4*>(base + (size_t)n * 32 + 8 * c) + 1);
-      if (w == 0) { lo4 = a; hi4 = b; }
-      else { lo4.x += a.x; lo4.y += a.y; lo4.z += a.z; lo4.w += a.w; hi4.x += b.x; hi4.y += b.y; hi4.z += b.z; hi4.w += b.w; }
-      if (boss) {
-        float vb;
-        asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(vb) : "l"(base + (size_t)L.H * 32) : "memory");
-        sb2 = w == 0 ? vb : sb2 + vb;
-      }
+    const float* mine = d.push[d.rank] + (int64_t)(e & 1) * d.world * d.cap;
+    g = ld_peer1(mine + xi);
+    if (boss) gb2 = ld_peer1(mine + xb2);
+    for (int w = 1; w < d.world; ++w) {
+      g += ld_peer1(mine + (int64_t)w * d.cap + xi);
+      if (boss) gb2 += ld_peer1(mine + (int64_t)w * d.cap + xb2);
     }
-    g[0] = lo4.x; g[1] = lo4.y; g[2] = lo4.z; g[3] = lo4.w; g[4] = hi4.x; g[5] = hi4.y; g[6] = hi4.z; g[7] = hi4.w;
-    gb2 = sb2;
     __syncthreads();
     if (threadIdx.x == 0) {
-      if (atomicAdd(&d.tickets[1], 1u) == gridDim.x - 1) {
+      if (atomicAdd(&d.tickets[1], 1u) == gridDim.x - 1) {   // the last CTA to have read its slots closes the epoch
         d.tickets[1] = 0u;
         *d.epoch = e;
         __threadfence();
@@ -912,51 +942,41 @@ mlp_update_tc_kernel(const float* __restrict__ partial, const float* __restrict_
   } else {
     __syncthreads();                                     // sh[] written
   }
-  // ---- Adam on the parameters this thread owns; the summed gradient goes back to the flat bucket
+  // ---- Adam on the parameter this thread owns; the (summed) gradient goes back to the flat bucket
   const float neg_step_size = sh[0], bc2_sqrt = sh[1];
-  float b1_new = b1, w2_new = w2;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int k = 8 * c + j;
-    int64_t idx = -1;
-    if (k < F) idx = L.off_w1() + (int64_t)n * F + k;
-    else if (k == F) idx = L.off_b1() + n;
-    else if (k == F + 1) idx = L.off_w2() + n;
-    if (idx >= 0) {
-      float mm = m[idx], vv = v[idx];
-      grads[idx] = g[j];
-      adam_one(pw[j], g[j], mm, vv, s, neg_step_size, bc2_sqrt);
-      params[idx] = pw[j]; m[idx] = mm; v[idx] = vv;
-      if (k == F) b1_new = pw[j];
-      if (k == F + 1) w2_new = pw[j];
-    }
+  int64_t idx = -1;
+  if (lane < F) idx = L.off_w1() + (int64_t)n * F + lane;
+  else if (lane == F) idx = L.off_b1() + n;
+  else if (lane == F + 1) idx = L.off_w2() + n;
+  float pw = 0.f;
+  if (idx >= 0) {
+    pw = params[idx];
+    float mm = m[idx], vv = v[idx];
+    grads[idx] = g;
+    adam_one(pw, g, mm, vv, s, neg_step_size, bc2_sqrt);
+    params[idx] = pw; m[idx] = mm; v[idx] = vv;
   }
   if (boss) {
-    const int64_t idx = L.off_b2();
-    float pp = params[idx], mm = m[idx], vv = v[idx];
-    grads[idx] = gb2;
+    const int64_t ib = L.off_b2();
+    float pp = params[ib], mm = m[ib], vv = v[ib];
+    grads[ib] = gb2;
     adam_one(pp, gb2, mm, vv, s, neg_step_size, bc2_sqrt);
-    params[idx] = pp; m[idx] = mm; v[idx] = vv;
-    if (loss_part) {             // fused loss: mean over the batch, split partials summed in split order in double
-      double ls = 0.0;
-      for (int sp = 0; sp < n_splits; ++sp) ls += (double)loss_part[sp];
-      *loss_out = (float)(ls * inv_batch);
-    }
+    params[ib] = pp; m[ib] = mm; v[ib] = vv;
   }
   // ---- bf16 pack of the new W1 / b1 and the partials of v (pack_w1_kernel)
-  b1_new = __shfl_sync(0xffffffffu, b1_new, r8 + 8 * (F >> 3));
-  w2_new = __shfl_sync(0xffffffffu, w2_new, r8 + 8 * ((F + 1) >> 3));
-  (void)lane;
+  const float b1_new = __shfl_sync(0xffffffffu, pw, F);
+  const float w2_new = __shfl_sync(0xffffffffu, pw, F + 1);
   const __nv_bfloat16 hi = __float2bfloat16(b1_new);
   const __nv_bfloat16 lo = __float2bfloat16(b1_new - __bfloat162float(hi));
-  __nv_bfloat16 q[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int k = 8 * c + j;
-    q[j] = k < F ? __float2bfloat16(pw[j]) : (k == F ? hi : (k == F + 1 ? lo : __float2bfloat16(0.f)));
-    prod[rl][k] = w2_new * __bfloat162float(q[j]);
-  }
-  w1q[t] = *reinterpret_cast<uint4*>(q);
+  const __nv_bfloat16 q = lane < F ? __float2bfloat16(pw) : (lane == F ? hi : (lane == F + 1 ? lo : __float2bfloat16(0.f)));
+  prod[wib][lane] = w2_new * __bfloat162float(q);
+  // eight lanes' bf16 values -> one 16-byte store (the k chunk c = lane / 8 of row n)
+  uint32_t h16 = (uint32_t)__bfloat16_as_ushort(q);
+  uint32_t pair = h16 | (__shfl_down_sync(0xffffffffu, h16, 1) << 16);        // valid on even lanes
+  uint32_t pair2 = __shfl_down_sync(0xffffffffu, pair, 2);                     // lanes % 4 == 0: {pair, pair2} = 4 values
+  uint32_t q2 = __shfl_down_sync(0xffffffffu, pair, 4), q3 = __shfl_down_sync(0xffffffffu, pair2, 4);
+  if ((lane & 7) == 0)
+    *reinterpret_cast<uint4*>(w1q + tiled_byte(n, lane)) = make_uint4(pair, pair2, q2, q3);
   __syncthreads();
   if (threadIdx.x < 32) {
     float a = 0.f;
@@ -1041,28 +1061,20 @@ static int launch_gen_batch(void* xq_dev, float* y_dev, int64_t batch, int n_fea
   B200_REQUIRE(offset % 4 == 0, "gen_batch_bf16: offset must be a multiple of 4");
   B200_REQUIRE(xq_dev && y_dev, "gen_batch_bf16: null pointer");
   int grid, calls;
-  philox_plan(batch * n_features, &grid, &calls);
-  int64_t threads = batch * (KP / 8);
-  const unsigned blocks = (unsigned)((threads + 255) / 256);
+  philox_plan(batch * n_features, &grid, &calls);         // torch's own geometry: the kernel IS that grid
   const uint2 key = make_uint2((unsigned)seed, (unsigned)(seed >> 32));
   const bool small = batch * n_features < (int64_t)1 << 31;
-  const uint32_t inv = small ? (uint32_t)(((uint64_t)1 << 32) / ((uint64_t)grid * 256)) : 0u;
-#define B200_GEN_CASE(P)                                                                                                   \
-  case P:                                                                                                                  \
-    if (small)                                                                                                             \
-      gen_batch_kernel<uint32_t, P><<<blocks, 256, 0, as_stream(stream)>>>(                                                \
-          reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256, inv, calls,    \
-          reinterpret_cast<const unsigned long long*>(draw_counter_dev));                                                  \
-    else                                                                                                                   \
-      gen_batch_kernel<uint64_t, P><<<blocks, 256, 0, as_stream(stream)>>>(                                                \
-          reinterpret_cast<uint4*>(xq_dev), y_dev, batch, n_features, key, offset / 4, (int64_t)grid * 256, inv, calls,    \
-          reinterpret_cast<const unsigned long long*>(draw_counter_dev));                                                  \
-    break;
-  switch ((n_features + 3) >> 2) {
-    B200_GEN_CASE(1) B200_GEN_CASE(2) B200_GEN_CASE(3) B200_GEN_CASE(4)
-    B200_GEN_CASE(5) B200_GEN_CASE(6) B200_GEN_CASE(7) B200_GEN_CASE(8)
-  }
-#undef B200_GEN_CASE
+  const uint32_t nthreads = (uint32_t)grid * 256u;
+  auto inv32 = [](uint64_t d) { uint64_t q = ((uint64_t)1 << 32) / d; return (uint32_t)(q > 0xFFFFFFFFull ? 0xFFFFFFFFull : q); };   // d = 1: 2^32 - 1
+  const uint32_t inv_F = inv32((uint64_t)n_features), inv_nt = inv32((uint64_t)nthreads);
+  if (small)
+    gen_batch_kernel<uint32_t><<<grid, 256, 0, as_stream(stream)>>>(
+        reinterpret_cast<unsigned char*>(xq_dev), y_dev, batch, n_features, key, offset / 4, nthreads, calls, inv_F, inv_nt,
+        reinterpret_cast<const unsigned long long*>(draw_counter_dev));
+  else
+    gen_batch_kernel<uint64_t><<<grid, 256, 0, as_stream(stream)>>>(
+        reinterpret_cast<unsigned char*>(xq_dev), y_dev, batch, n_features, key, offset / 4, nthreads, calls, inv_F, inv_nt,
+        reinterpret_cast<const unsigned long long*>(draw_counter_dev));
   B200_LAUNCH_CHECK();
   if (offset_advance) *offset_advance = (uint64_t)calls * 4;
   return B200DS_OK;
@@ -1088,7 +1100,7 @@ int b200ds_pack_params_bf16(const float* params_dev, int n_features, int hidden,
   Layout L{n_features, hidden};
   unsigned char* w1q = reinterpret_cast<unsigned char*>(wq_dev);
   float* vpart = reinterpret_cast<float*>(w1q + (size_t)hidden * KP * 2);
-  pack_w1_kernel<<<hidden / kPackRows, 256, 0, as_stream(stream)>>>(params_dev, L, reinterpret_cast<uint4*>(wq_dev), vpart);
+  pack_w1_kernel<<<hidden / kPackRows, 4 * kPackRows, 0, as_stream(stream)>>>(params_dev, L, reinterpret_cast<uint4*>(wq_dev), vpart);
   B200_LAUNCH_CHECK();
   return B200DS_OK;
 }
@@ -1233,6 +1245,7 @@ int b200ds_update_tc(b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_by
   B200_REQUIRE(W == 1 || ctx->p2p_cap >= b200ds_update_tc_exchange_elems(hidden),
                "update_tc: %d ranks need b200ds_ctx_enable_p2p(ctx, >= %lld) first", W,
                (long long)b200ds_update_tc_exchange_elems(hidden));
+  if (W > 1) { if (int rc = p2p_check_mailbox(ctx, "update_tc")) return rc; }
   Layout L{n_features, hidden};
   const float* partial = reinterpret_cast<const float*>(scratch_dev);
   const float* db2_part = partial + (size_t)bp.splits * hidden * 32;
@@ -1241,17 +1254,19 @@ int b200ds_update_tc(b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_by
   float* vpart = reinterpret_cast<float*>(w1q + (size_t)hidden * KP * 2);
   const AdamScalars s = make_adam_scalars(beta1, beta2, eps, W > 1 ? (float)(1.0 / W) : 1.f);
   const P2PDev d = make_p2p_dev(ctx);
-  const int grid = hidden / kPackRows;                   // all resident at once (<= 128 for H <= 8192): they wait on each other
-  B200_REQUIRE(W == 1 || grid <= sm_count(), "update_tc: H = %d needs more CTAs than the GPU can keep resident", hidden);
-  if (step_counter_dev)
-    mlp_update_tc_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(
-        partial, db2_part, loss_part, bp.splits, 1.0 / (double)batch, params_dev, grads_dev, exp_avg_dev, exp_avg_sq_dev, L,
-        reinterpret_cast<uint4*>(wq_dev), vpart, s, lr, beta1, beta2, 0,
-        reinterpret_cast<const unsigned long long*>(step_counter_dev), loss_dev, d);
-  else
-    mlp_update_tc_kernel<false><<<grid, 256, 0, as_stream(stream)>>>(
-        partial, db2_part, loss_part, bp.splits, 1.0 / (double)batch, params_dev, grads_dev, exp_avg_dev, exp_avg_sq_dev, L,
-        reinterpret_cast<uint4*>(wq_dev), vpart, s, lr, beta1, beta2, step, nullptr, loss_dev, d);
+  const int grid = hidden / kPackRows, threads = 32 * kPackRows;
+  const unsigned long long* ctr = reinterpret_cast<const unsigned long long*>(step_counter_dev);
+  cudaStream_t st = as_stream(stream);
+#define B200_UPD(COUNTED, PHASE)                                                                                        \
+  mlp_update_tc_kernel<COUNTED, PHASE><<<grid, threads, 0, st>>>(partial, db2_part, loss_part, bp.splits, 1.0 / (double)batch, \
+      params_dev, grads_dev, exp_avg_dev, exp_avg_sq_dev, L, w1q, vpart, s, lr, beta1, beta2, COUNTED ? 0 : step, COUNTED ? ctr : nullptr, loss_dev, d)
+  if (W == 1) {
+    if (ctr) B200_UPD(true, 0); else B200_UPD(false, 0);
+  } else {
+    if (ctr) { B200_UPD(true, 1); B200_LAUNCH_CHECK(); B200_UPD(true, 2); }
+    else { B200_UPD(false, 1); B200_LAUNCH_CHECK(); B200_UPD(false, 2); }
+  }
+#undef B200_UPD
   B200_LAUNCH_CHECK();
   return B200DS_OK;
 }

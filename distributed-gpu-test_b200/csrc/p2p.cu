@@ -129,7 +129,7 @@ static void p2p_teardown(b200ds_ctx* ctx) {
 
 // The local half of the set-up; on failure the caller still takes part in the vote below.
 static int p2p_local_setup(b200ds_ctx* ctx, int64_t cap, void** words) {
-  B200_CUDA(cudaMalloc(&ctx->p2p_xchg[ctx->rank], sizeof(float) * 2 * (size_t)cap));
+  B200_CUDA(cudaMalloc(&ctx->p2p_xchg[ctx->rank], sizeof(float) * 2 * (size_t)cap * (size_t)(1 + ctx->world)));   // pull region + one push slot per rank, two halves each
   B200_CUDA(cudaMalloc(words, 256));      // flag row (W x u64) | epoch (u64) | tickets (2 x u32)
   ctx->p2p_flags[ctx->rank] = reinterpret_cast<unsigned long long*>(*words);
   B200_CUDA(cudaMemset(*words, 0, 256));
@@ -228,7 +228,7 @@ int b200ds_ctx_enable_p2p(b200ds_ctx* ctx, int64_t max_elems) {
 }
 
 // A wait that timed out in an earlier launch left a note in the mailbox (and a trapped context).
-static int p2p_check_mailbox(const b200ds_ctx* ctx, const char* who) {
+int p2p_check_mailbox(const b200ds_ctx* ctx, const char* who) {
   if (ctx->p2p_mailbox && ctx->p2p_mailbox[0] != 0ull) {
     set_error("%s: an earlier exchange on rank %d gave up waiting for rank %d at epoch %llu (B200DS_P2P_TIMEOUT_MS = %llu)", who,
               ctx->rank, (int)(ctx->p2p_mailbox[0] - 1ull), ctx->p2p_mailbox[1], ctx->p2p_timeout_ns / 1000000ull);

@@ -4,12 +4,16 @@
 #include "ctx.cuh"
 #include <string.h>
 
+// p2p.cu: a flag wait that timed out in an earlier launch left a note in the context's mailbox (not exported)
+extern "C" int p2p_check_mailbox(const b200ds_ctx* ctx, const char* who);
+
 namespace b200ds {
 
 struct P2PDev {
   int world, rank;
   int64_t cap;                              // floats per half of an exchange buffer
-  float* xchg[B200DS_P2P_MAX_WORLD];        // every rank's exchange buffer (own entry = local memory)
+  float* xchg[B200DS_P2P_MAX_WORLD];        // every rank's exchange buffer (own entry = local memory): [2 halves][cap], pulled from
+  float* push[B200DS_P2P_MAX_WORLD];        // the part of it the peers store into: [2 halves][world slots][cap], slot r written by rank r
   unsigned long long* flags[B200DS_P2P_MAX_WORLD];   // every rank's flag row: flags[p][r] = last epoch rank r published to p
   unsigned long long* epoch;                // local: epochs completed
   unsigned int* tickets;                    // local: [0] copy-phase arrivals, [1] exit arrivals
@@ -38,6 +42,12 @@ __device__ __forceinline__ float4 ld_peer(const float4* p) {
   return v;
 }
 
+__device__ __forceinline__ float ld_peer1(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+
 // Wait until *flag >= e.  Ranks drift apart by far more than a spin count covers (first-call module load, a graph
 // capture, rank 0 writing a checkpoint), so the bound is wall time on %globaltimer, generous and configurable.  A
 // wait that still runs out says which rank it waited for in the pinned mailbox (readable by the host after the
@@ -49,7 +59,11 @@ inline P2PDev make_p2p_dev(const b200ds_ctx* ctx) {
   P2PDev d;
   memset(&d, 0, sizeof(d));
   d.world = ctx->world; d.rank = ctx->rank; d.cap = ctx->p2p_cap;
-  for (int w = 0; w < ctx->world; ++w) { d.xchg[w] = ctx->p2p_xchg[w]; d.flags[w] = ctx->p2p_flags[w]; }
+  for (int w = 0; w < ctx->world; ++w) {
+    d.xchg[w] = ctx->p2p_xchg[w];
+    d.push[w] = ctx->p2p_xchg[w] ? ctx->p2p_xchg[w] + 2 * ctx->p2p_cap : nullptr;
+    d.flags[w] = ctx->p2p_flags[w];
+  }
   unsigned long long* words = ctx->p2p_flags[ctx->rank];
   if (words) {
     d.epoch = words + B200DS_P2P_MAX_WORLD;
