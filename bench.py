@@ -270,7 +270,7 @@ class WideStep:
                           % lib.b200ds_last_error().decode("utf-8", "replace"), file=sys.stderr, flush=True)
                 self.p2p = False
                 self.fused_update = False
-        self.side = torch.cuda.Stream(device=dev)
+        self.side = torch.cuda.Stream(device=dev, priority=-1)     # the exchange: its CTAs go first whenever an SM has room
 
     @property
     def launches(self):
@@ -278,7 +278,7 @@ class WideStep:
         if not self.tc:
             return 7                      # philox, label, forward, loss, backward, finish, adam
         if self.fused_update:
-            return 4 if self.world == 1 else 5     # gen_batch, forward, loss+backward, update (publish + collect for W > 1)
+            return 4 if self.world == 1 else 6     # gen_batch, forward, loss+backward, update (W > 1: publish, gate, collect)
         return 6                                   # ... finish, adam (or exchange+adam), pack_w1
 
     def step(self, st, ev_pair=None):
@@ -328,18 +328,21 @@ class WideStep:
         if self.tc and self.fused_update:
             # finish pass + gradient exchange (W > 1, peer memory) + Adam + operand pack: one kernel.  With several
             # ranks it mostly waits on NVLink round trips, so it runs on a side stream beside the generator.
-            def update(stream_handle):
-                chk(lib.b200ds_update_tc(self.ctx, self.bwd_sc.data_ptr(), self.bwd_sc.numel(), B, F, H, self.params.data_ptr(),
-                                         self.grads.data_ptr(), self.m.data_ptr(), self.v.data_ptr(), self.wq.data_ptr(),
-                                         LR, 0.9, 0.999, 1e-8, 0, self.counter.data_ptr(), self.loss.data_ptr(), stream_handle))
+            def update(fn, stream_handle):
+                chk(fn(self.ctx, self.bwd_sc.data_ptr(), self.bwd_sc.numel(), B, F, H, self.params.data_ptr(),
+                       self.grads.data_ptr(), self.m.data_ptr(), self.v.data_ptr(), self.wq.data_ptr(),
+                       LR, 0.9, 0.999, 1e-8, 0, self.counter.data_ptr(), self.loss.data_ptr(), stream_handle))
             if self.world == 1:
-                update(st)
+                update(lib.b200ds_update_tc, st)
                 self.gen_next(st)
                 return
+            # several ranks: the gradients are published right behind the backward; the wait for the other ranks, the
+            # rank-order sum, Adam and the pack go to the (high-priority) side stream, the next batch is drawn meanwhile
+            update(lib.b200ds_update_tc_begin, st)
             main = torch.cuda.current_stream()
             fork = torch.cuda.Event(); fork.record(main)
             self.side.wait_event(fork)
-            update(self.side.cuda_stream)
+            update(lib.b200ds_update_tc_end, self.side.cuda_stream)
             join = torch.cuda.Event(); join.record(self.side)
             self.gen_next(st)
             main.wait_event(join)
@@ -496,15 +499,17 @@ def run_ours(a):
         graph.reset()          # NCCL will not tear a communicator down while a captured graph still refers to it
         del graph
         trace("kernel pass done")
+        if world > 1:
+            out["xrank"] = cross_rank_checks(ws, st, dev, world)
+            trace("cross-rank checks done")
         e2e = bench_e2e(lib, ctx, dev, wl, world, a, barrier, precision)
         trace("e2e done")
         out.update(dict(value=value, ms_per_step=ms_per_step, roofline=roof, e2e=e2e, clocks=clk.summary(),
                         gpu_launches=K * ws.launches, wall_s=wall, loss_last=loss_last,
-                        config={"workload": f"{a.workload}: train.py step, F={wl['F']} H={wl['H']}, {wl['B']} samples/GPU/step "
-                                            f"generated on device (Philox4x32-10), Adam, {world} rank(s)",
-                                "per_gpu_batch": wl["B"], "n_features": wl["F"], "hidden": wl["H"], "parallelism": f"dp{world}",
+                        config={**workload_config(a.workload, wl, world),
                                 "l2": "256 MiB device buffer rewritten between timed steps, outside the per-step CUDA-event brackets",
-                                "exchange": ("peer-memory all-reduce + Adam in one kernel (b200ds_allreduce_adam_p2p)" if ws.p2p else
+                                "exchange": (("finish + push over peer memory + Adam + pack (b200ds_update_tc, two launches)" if ws.fused_update else
+                                              "peer-memory all-reduce + Adam in one kernel (b200ds_allreduce_adam_p2p)") if ws.p2p else
                                              "ncclAllReduce on a side stream + Adam kernel") if world > 1 else "none (1 rank)",
                                 "timing": "each step = one CUDA-graph replay of the whole step (all kernels + the gradient exchange), "
                                           "bracketed by CUDA events on the launching stream; sum over steps, max over ranks"},
@@ -535,6 +540,58 @@ def run_ours(a):
             dist.destroy_process_group()
         except Exception:       # noqa: BLE001
             pass
+
+
+def cross_rank_checks(ws, st, dev, world):
+    """Outside the timed region, N > 1: (1) the replicas are bit-equal -- a 64-bit checksum of the whole parameter
+    vector and a 1 KB sample, all-gathered and compared on every rank; (2) the exchange bench.py runs (peer memory)
+    against the NCCL arm: 3 more steps from the same state with each, largest relative parameter difference
+    (the peer kernel sums in rank order, NCCL in ring/tree order: round-off only).  train.py:113-114."""
+    import torch.distributed as dist
+    P = ws.P
+
+    def fingerprint():
+        torch.cuda.synchronize()
+        bits = ws.params[:P].view(torch.int32).to(torch.int64)
+        chk = torch.stack([bits.sum(), (bits * (torch.arange(P, device=dev) % 8191 + 1)).sum()])
+        sample = ws.params[:256].view(torch.int32).to(torch.int64)
+        mine = torch.cat([chk, sample])
+        allr = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        return all(torch.equal(allr[0], a) for a in allr), int(chk[0])
+
+    equal, chk = fingerprint()
+    res = {"params_bit_equal_across_ranks": bool(equal), "params_checksum": chk}
+    if ws.tc:
+        keep = {k: getattr(ws, k).clone() for k in ("params", "grads", "m", "v", "xq", "y", "wq", "counter", "loss")}
+
+        def restore():
+            for k, t in keep.items():
+                getattr(ws, k).copy_(t)
+            torch.cuda.synchronize()
+            dist.barrier()
+
+        arm = (ws.p2p, ws.fused_update)
+        for _ in range(3):
+            ws.step(st)
+        eq2, _ = fingerprint()
+        ours = ws.params[:P].clone()
+        restore()
+        ws.p2p, ws.fused_update = False, False           # ncclAllReduce on the side stream + the Adam kernel + the pack kernel
+        for _ in range(3):
+            ws.step(st)
+        torch.cuda.synchronize()
+        ref = ws.params[:P]
+        res.update({"extra_steps": 3, "bit_equal_after_extra_steps": bool(eq2),
+                    "exchange_vs_nccl_max_rel_diff": float(((ours - ref).abs() / ref.abs().clamp_min(1e-6)).max()),
+                    "exchange_vs_nccl_max_abs_diff": float((ours - ref).abs().max()),
+                    "exchange": "b200ds_update_tc (push over peer memory)" if arm[1] else
+                                ("b200ds_allreduce_adam_p2p" if arm[0] else "ncclAllReduce")})
+        restore()
+        ws.p2p, ws.fused_update = arm
+    if not equal:
+        raise RuntimeError("replicas differ across ranks after the timed region: %r" % (res,))
+    return res
 
 
 def _nccl_id(lib):
@@ -594,7 +651,23 @@ def bench_e2e(lib, ctx, dev, wl, world, a, barrier, precision):
     t = torch.tensor([dt], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return dict(value=world * B * K / float(t), unit="samples/s", h2d_bytes_per_step=4 * (B * F + B), d2h_bytes_per_step=4,
+    # the same host->device copies alone, all ranks at once: what the box's host side can feed (the e2e step needs
+    # 5.5 MB per rank per step; with 8 ranks the copies share the host's memory and PCIe root complexes)
+    barrier()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
+    for i in range(K):
+        xs[: B * F].copy_(xh[i % nbuf].view(-1), non_blocking=True)
+        ys[:B].copy_(yh[i % nbuf].view(-1), non_blocking=True)
+    c1.record()
+    barrier()
+    tc_ = torch.tensor([c0.elapsed_time(c1) / 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tc_, op=dist.ReduceOp.MAX)
+    h2d = 4 * (B * F + B)
+    return dict(value=world * B * K / float(t), unit="samples/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=4,
+                h2d_gbs_per_gpu=h2d * K / float(t) / 1e9, h2d_only_gbs_per_gpu=h2d * K / float(tc_) / 1e9,
+                h2d_only_samples_per_s=world * B * K / float(tc_),
                 steps=K, api="b200ds_train_step_host_prefetch (C ABI, pinned host x/y in, host loss out, stream sync per step; "
                 "the copy of batch k+1 is issued on a copy stream before batch k is computed)",
                 loss_last=float(lh))

@@ -86,6 +86,10 @@ PROTOTYPES = {
     "b200ds_update_tc_exchange_elems": (c_i64, [C.c_int]),
     "b200ds_update_tc": (C.c_int, [c_ptr, c_ptr, C.c_size_t, c_i64, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                                    C.c_double, C.c_double, C.c_double, C.c_double, c_i64, c_ptr, c_ptr, c_stream]),
+    "b200ds_update_tc_begin": (C.c_int, [c_ptr, c_ptr, C.c_size_t, c_i64, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                                         C.c_double, C.c_double, C.c_double, C.c_double, c_i64, c_ptr, c_ptr, c_stream]),
+    "b200ds_update_tc_end": (C.c_int, [c_ptr, c_ptr, C.c_size_t, c_i64, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                                       C.c_double, C.c_double, C.c_double, C.c_double, c_i64, c_ptr, c_ptr, c_stream]),
     "b200ds_ctx_enable_p2p": (C.c_int, [c_ptr, c_i64]),
     "b200ds_allreduce_adam_p2p": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, C.c_double, C.c_double, C.c_double,
                                             C.c_double, c_i64, c_ptr, c_stream]),

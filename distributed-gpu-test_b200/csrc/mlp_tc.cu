@@ -113,10 +113,13 @@ gen_batch_kernel(unsigned char* __restrict__ xq, float* __restrict__ y, int64_t 
   __shared__ float xs[kGenMaxCalls * 4][256 + kGenHaloMax];
   if (draw_counter) ctr0 += (uint64_t)(*draw_counter) * (uint64_t)calls;
   const int t = threadIdx.x;
-  const uint32_t sub = blockIdx.x * 256u + t;
   const idx_t n = (idx_t)batch * (idx_t)F;
   const int half = F >> 1, halo = F - 1;
+  // a CTA walks torch's blocks vb = blockIdx.x, blockIdx.x + gridDim.x, ...: the launch may hold fewer CTAs than torch's
+  // grid so that the generator leaves room on every SM for the kernels it runs beside (the gradient exchange)
+  for (uint32_t vb = blockIdx.x; vb < nthreads / 256u; vb += gridDim.x)
   for (int c0 = 0; c0 < calls; c0 += kGenMaxCalls) {
+    const uint32_t sub = vb * 256u + t;
     const int nc = min(kGenMaxCalls, calls - c0);
     // ---- this thread's elements: up to kGenMaxCalls independent Philox chains side by side
     float val[kGenMaxCalls][4];
@@ -135,7 +138,7 @@ gen_batch_kernel(unsigned char* __restrict__ xq, float* __restrict__ y, int64_t 
     }
     // ---- halo: the `halo` elements after the block's 256, per (c, i)
     if (t < halo) {
-      const uint32_t sub_h = blockIdx.x * 256u + 256u + t;
+      const uint32_t sub_h = vb * 256u + 256u + t;
       if (sub_h < nthreads) {              // same call index, next subsequences: one evaluation serves i = 0..3
         for (int cc = 0; cc < nc; ++cc) {
           float hv[4] = {0.f, 0.f, 0.f, 0.f};
@@ -166,7 +169,7 @@ gen_batch_kernel(unsigned char* __restrict__ xq, float* __restrict__ y, int64_t 
     for (int w = t; w < nc * 4 * rows_per * (KP / 8); w += 256) {
       const int c8 = w & (KP / 8 - 1), wr = w >> 2;                    // KP / 8 == 4
       const int combo = wr / rows_per, ri = wr - combo * rows_per;
-      const idx_t base = (idx_t)blockIdx.x * 256 + (idx_t)nthreads * (idx_t)(4 * c0 + combo);
+      const idx_t base = (idx_t)vb * 256 + (idx_t)nthreads * (idx_t)(4 * c0 + combo);
       if (base >= n) continue;
       idx_t row0; uint32_t k0;
       gen_divmod<idx_t>(base, (uint32_t)F, inv_F, &row0, &k0);
@@ -837,10 +840,12 @@ mlp_bwd_tc_finish(const float* __restrict__ partial, const float* __restrict__ d
 //   kPhase 1  several ranks, first launch: finish pass, then the gradients are PUSHED: every rank stores its own into
 //             slot `rank` of every rank's exchange buffer (its own included), layout [unit][32] + db2, then -- last CTA
 //             of the grid -- the epoch into its flag at every peer;
-//   kPhase 2  second launch: wait for every rank's flag (they sit in local memory), add the W slots up in rank order
-//             (local reads only: the data crossed NVLink one way, once), Adam, pack.
-// Two launches because a CTA of phase 2 waits for OTHER GPUs only, never for a CTA of its own grid: no CTA has to be
-// resident for another one to make progress, so the grid can be as large as the work wants.
+//   (gate)    a one-warp kernel waits for every rank's flag (they sit in local memory): while the ranks wait for the
+//             slowest of them nothing but this warp is resident, the SMs belong to whatever runs beside the exchange;
+//   kPhase 2  last launch: add the W slots up in rank order (local reads only: the data crossed NVLink one way,
+//             once), Adam, pack.
+// Separate launches because nothing here waits for a CTA of its own grid: no CTA has to be resident for another one to
+// make progress, so the grids can be as large as the work wants.
 template <bool kCounted, int kPhase>
 __global__ void __launch_bounds__(32 * kPackRows)
 mlp_update_tc_kernel(const float* __restrict__ partial, const float* __restrict__ db2_part, const float* __restrict__ loss_part,
@@ -921,9 +926,7 @@ mlp_update_tc_kernel(const float* __restrict__ partial, const float* __restrict_
     return;
   }
   if (kPhase == 2) {
-    const unsigned long long e = *d.epoch + 1;
-    if (threadIdx.x < d.world) p2p_wait_flag(&d.flags[d.rank][threadIdx.x], e, (int)threadIdx.x, d);
-    __syncthreads();
+    const unsigned long long e = *d.epoch + 1;             // the gate kernel before this launch has seen every rank's flag at e
     const float* mine = d.push[d.rank] + (int64_t)(e & 1) * d.world * d.cap;
     g = ld_peer1(mine + xi);
     if (boss) gb2 = ld_peer1(mine + xb2);
@@ -983,6 +986,12 @@ mlp_update_tc_kernel(const float* __restrict__ partial, const float* __restrict_
     for (int r = 0; r < kPackRows; ++r) a += prod[r][threadIdx.x];
     vpart[(size_t)blockIdx.x * 32 + threadIdx.x] = a;
   }
+}
+
+__global__ void __launch_bounds__(32)
+p2p_gate_kernel(P2PDev d) {
+  const unsigned long long e = *d.epoch + 1;
+  if (threadIdx.x < d.world) p2p_wait_flag(&d.flags[d.rank][threadIdx.x], e, (int)threadIdx.x, d);
 }
 
 // ------------------------------------------------------------------ host side
@@ -1067,12 +1076,14 @@ static int launch_gen_batch(void* xq_dev, float* y_dev, int64_t batch, int n_fea
   const uint32_t nthreads = (uint32_t)grid * 256u;
   auto inv32 = [](uint64_t d) { uint64_t q = ((uint64_t)1 << 32) / d; return (uint32_t)(q > 0xFFFFFFFFull ? 0xFFFFFFFFull : q); };   // d = 1: 2^32 - 1
   const uint32_t inv_F = inv32((uint64_t)n_features), inv_nt = inv32((uint64_t)nthreads);
+  static const int ctas_per_sm = getenv("B200DS_GEN_CTAS_PER_SM") ? atoi(getenv("B200DS_GEN_CTAS_PER_SM")) : 8;   // tuning: 8 = torch's own grid
+  const int lgrid = grid < sm_count() * ctas_per_sm ? grid : sm_count() * ctas_per_sm;
   if (small)
-    gen_batch_kernel<uint32_t><<<grid, 256, 0, as_stream(stream)>>>(
+    gen_batch_kernel<uint32_t><<<lgrid, 256, 0, as_stream(stream)>>>(
         reinterpret_cast<unsigned char*>(xq_dev), y_dev, batch, n_features, key, offset / 4, nthreads, calls, inv_F, inv_nt,
         reinterpret_cast<const unsigned long long*>(draw_counter_dev));
   else
-    gen_batch_kernel<uint64_t><<<grid, 256, 0, as_stream(stream)>>>(
+    gen_batch_kernel<uint64_t><<<lgrid, 256, 0, as_stream(stream)>>>(
         reinterpret_cast<unsigned char*>(xq_dev), y_dev, batch, n_features, key, offset / 4, nthreads, calls, inv_F, inv_nt,
         reinterpret_cast<const unsigned long long*>(draw_counter_dev));
   B200_LAUNCH_CHECK();
@@ -1227,25 +1238,26 @@ int b200ds_mlp_loss_backward_partials_tc(const void* xq_dev, const void* wq_dev,
 
 int64_t b200ds_update_tc_exchange_elems(int hidden) { return (int64_t)hidden * 32 + 4; }
 
-int b200ds_update_tc(b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_bytes, int64_t batch, int n_features, int hidden,
-                     float* params_dev, float* grads_dev, float* exp_avg_dev, float* exp_avg_sq_dev, void* wq_dev,
-                     double lr, double beta1, double beta2, double eps, int64_t step, const uint64_t* step_counter_dev,
-                     float* loss_dev, uintptr_t stream) {
-  B200_REQUIRE(ctx != nullptr, "update_tc: null context");
+// which = 1: finish + publish (or the whole update for one rank), 2: gate + collect + Adam + pack, 3: both
+static int launch_update_tc(int which, const char* who, b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_bytes, int64_t batch,
+                            int n_features, int hidden, float* params_dev, float* grads_dev, float* exp_avg_dev,
+                            float* exp_avg_sq_dev, void* wq_dev, double lr, double beta1, double beta2, double eps, int64_t step,
+                            const uint64_t* step_counter_dev, float* loss_dev, uintptr_t stream) {
+  B200_REQUIRE(ctx != nullptr, "%s: null context", who);
   B200_REQUIRE(tc_shape_ok(batch, n_features, hidden),
-               "update_tc: needs F <= %d, H %% 128 == 0, batch %% 128 == 0 (got B=%lld F=%d H=%d)", KP - 2,
+               "%s: needs F <= %d, H %% 128 == 0, batch %% 128 == 0 (got B=%lld F=%d H=%d)", who, KP - 2,
                (long long)batch, n_features, hidden);
-  B200_REQUIRE(params_dev && grads_dev && exp_avg_dev && exp_avg_sq_dev && wq_dev, "update_tc: null pointer");
-  B200_REQUIRE(step_counter_dev != nullptr || step >= 1, "update_tc: step must be >= 1 (t after the increment)");
+  B200_REQUIRE(params_dev && grads_dev && exp_avg_dev && exp_avg_sq_dev && wq_dev, "%s: null pointer", who);
+  B200_REQUIRE(step_counter_dev != nullptr || step >= 1, "%s: step must be >= 1 (t after the increment)", who);
   BwdPlan bp;
   bwd_plan(batch, hidden, &bp);
   size_t need = b200ds_mlp_backward_tc_scratch_bytes(batch, n_features, hidden);
-  B200_REQUIRE(scratch_dev && scratch_bytes >= need, "update_tc: scratch too small (%zu < %zu)", scratch_bytes, need);
+  B200_REQUIRE(scratch_dev && scratch_bytes >= need, "%s: scratch too small (%zu < %zu)", who, scratch_bytes, need);
   const int W = ctx->world;
   B200_REQUIRE(W == 1 || ctx->p2p_cap >= b200ds_update_tc_exchange_elems(hidden),
-               "update_tc: %d ranks need b200ds_ctx_enable_p2p(ctx, >= %lld) first", W,
+               "%s: %d ranks need b200ds_ctx_enable_p2p(ctx, >= %lld) first", who, W,
                (long long)b200ds_update_tc_exchange_elems(hidden));
-  if (W > 1) { if (int rc = p2p_check_mailbox(ctx, "update_tc")) return rc; }
+  if (W > 1) { if (int rc = p2p_check_mailbox(ctx, who)) return rc; }
   Layout L{n_features, hidden};
   const float* partial = reinterpret_cast<const float*>(scratch_dev);
   const float* db2_part = partial + (size_t)bp.splits * hidden * 32;
@@ -1261,14 +1273,42 @@ int b200ds_update_tc(b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_by
   mlp_update_tc_kernel<COUNTED, PHASE><<<grid, threads, 0, st>>>(partial, db2_part, loss_part, bp.splits, 1.0 / (double)batch, \
       params_dev, grads_dev, exp_avg_dev, exp_avg_sq_dev, L, w1q, vpart, s, lr, beta1, beta2, COUNTED ? 0 : step, COUNTED ? ctr : nullptr, loss_dev, d)
   if (W == 1) {
-    if (ctr) B200_UPD(true, 0); else B200_UPD(false, 0);
+    if (which & 1) { if (ctr) B200_UPD(true, 0); else B200_UPD(false, 0); }
   } else {
-    if (ctr) { B200_UPD(true, 1); B200_LAUNCH_CHECK(); B200_UPD(true, 2); }
-    else { B200_UPD(false, 1); B200_LAUNCH_CHECK(); B200_UPD(false, 2); }
+    if (which & 1) { if (ctr) B200_UPD(true, 1); else B200_UPD(false, 1); B200_LAUNCH_CHECK(); }
+    if (which & 2) {
+      p2p_gate_kernel<<<1, 32, 0, st>>>(d);
+      B200_LAUNCH_CHECK();
+      if (ctr) B200_UPD(true, 2); else B200_UPD(false, 2);
+    }
   }
 #undef B200_UPD
   B200_LAUNCH_CHECK();
   return B200DS_OK;
+}
+
+int b200ds_update_tc(b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_bytes, int64_t batch, int n_features, int hidden,
+                     float* params_dev, float* grads_dev, float* exp_avg_dev, float* exp_avg_sq_dev, void* wq_dev,
+                     double lr, double beta1, double beta2, double eps, int64_t step, const uint64_t* step_counter_dev,
+                     float* loss_dev, uintptr_t stream) {
+  return launch_update_tc(3, "update_tc", ctx, scratch_dev, scratch_bytes, batch, n_features, hidden, params_dev, grads_dev, exp_avg_dev,
+                          exp_avg_sq_dev, wq_dev, lr, beta1, beta2, eps, step, step_counter_dev, loss_dev, stream);
+}
+
+int b200ds_update_tc_begin(b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_bytes, int64_t batch, int n_features, int hidden,
+                           float* params_dev, float* grads_dev, float* exp_avg_dev, float* exp_avg_sq_dev, void* wq_dev,
+                           double lr, double beta1, double beta2, double eps, int64_t step, const uint64_t* step_counter_dev,
+                           float* loss_dev, uintptr_t stream) {
+  return launch_update_tc(1, "update_tc_begin", ctx, scratch_dev, scratch_bytes, batch, n_features, hidden, params_dev, grads_dev,
+                          exp_avg_dev, exp_avg_sq_dev, wq_dev, lr, beta1, beta2, eps, step, step_counter_dev, loss_dev, stream);
+}
+
+int b200ds_update_tc_end(b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_bytes, int64_t batch, int n_features, int hidden,
+                         float* params_dev, float* grads_dev, float* exp_avg_dev, float* exp_avg_sq_dev, void* wq_dev,
+                         double lr, double beta1, double beta2, double eps, int64_t step, const uint64_t* step_counter_dev,
+                         float* loss_dev, uintptr_t stream) {
+  return launch_update_tc(2, "update_tc_end", ctx, scratch_dev, scratch_bytes, batch, n_features, hidden, params_dev, grads_dev,
+                          exp_avg_dev, exp_avg_sq_dev, wq_dev, lr, beta1, beta2, eps, step, step_counter_dev, loss_dev, stream);
 }
 
 }  // extern "C"

@@ -294,6 +294,21 @@ B200DS_API int b200ds_update_tc(b200ds_ctx* ctx, const void* scratch_dev, size_t
                                 float* exp_avg_dev, float* exp_avg_sq_dev, void* wq_dev, double lr, double beta1,
                                 double beta2, double eps, int64_t step, const uint64_t* step_counter_dev,
                                 float* loss_dev, uintptr_t stream);
+/* The same update in two halves, same arguments, possibly on different streams (the caller orders `_end` after
+ * `_begin` with an event): `_begin` = finish pass + publication of this rank's gradients in every rank's
+ * exchange buffer (for one rank: the whole update); `_end` = wait for every rank's publication (a one-warp
+ * kernel, so the SMs stay free for work enqueued beside it, e.g. the next batch's generation), rank-order sum,
+ * Adam, operand pack (for one rank: nothing).  b200ds_update_tc = both, back to back. */
+B200DS_API int b200ds_update_tc_begin(b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_bytes, int64_t batch,
+                                int n_features, int hidden, float* params_dev, float* grads_dev,
+                                float* exp_avg_dev, float* exp_avg_sq_dev, void* wq_dev, double lr, double beta1,
+                                double beta2, double eps, int64_t step, const uint64_t* step_counter_dev,
+                                float* loss_dev, uintptr_t stream);
+B200DS_API int b200ds_update_tc_end(b200ds_ctx* ctx, const void* scratch_dev, size_t scratch_bytes, int64_t batch,
+                                int n_features, int hidden, float* params_dev, float* grads_dev,
+                                float* exp_avg_dev, float* exp_avg_sq_dev, void* wq_dev, double lr, double beta1,
+                                double beta2, double eps, int64_t step, const uint64_t* step_counter_dev,
+                                float* loss_dev, uintptr_t stream);
 
 /* ---- end-to-end step with HOST buffers (what bench.py's `e2e` times) ---------------
  * One call = train.py:104-115 for one batch: H2D of x,y from (pinned) host memory,
