@@ -67,11 +67,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded: a protocol bug must not hang the GPU box (traps instead).
+// Bounded in wall time: a protocol bug must not hang the GPU box (traps after ~4 s instead; with the suspend hint a
+// spin count alone would bound nothing, one try can sleep for 10 ms).
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 20)) { __trap(); }
+    if ((++spins & 15u) == 0) {
+      unsigned long long t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > 4000000000ull) __trap();
+    }
   }
 }
 

@@ -310,6 +310,37 @@ B200DS_API int b200ds_update_tc_end(b200ds_ctx* ctx, const void* scratch_dev, si
                                 double beta2, double eps, int64_t step, const uint64_t* step_counter_dev,
                                 float* loss_dev, uintptr_t stream);
 
+/* ---- wide inputs: the widened model with n_features in the hundreds or thousands ("F = H", BASELINE config 4) --
+ * SimpleNet takes any n_features (train.py:26-33); from F = 256 on layer 1 is a real GEMM and runs as K-loop
+ * tcgen05.mma kernels fed by tensor-map TMA (csrc/mlp_fh.cu).  Shape class: F % 256 == 0, H % 128 == 0,
+ * batch % 256 == 0 (b200ds_fh_supported).  Semantics: GEMM operands rounded to bf16, fp32 accumulation, fp32
+ * master weights; the hidden activation is kept as bf16 between forward and backward (no recompute).
+ * Operands are bf16 arrays in "layout L" (8 x 8 core matrices, see mlp_fh.cu): b200ds_fh_operand_bytes(rows, cols)
+ * bytes each;  x: [batch, F], W1: [H, F], hT: [H, batch] (written by the forward, consumed by the backward).
+ * b200ds_fh_pack_bf16 converts a row-major fp32 matrix (rows % 8 == 0, cols % 64 == 0). */
+B200DS_API int b200ds_fh_supported(int64_t batch, int n_features, int hidden);
+B200DS_API size_t b200ds_fh_operand_bytes(int64_t rows, int64_t cols);
+B200DS_API int b200ds_fh_pack_bf16(const float* src_dev, int64_t rows, int64_t cols, void* dst_dev, uintptr_t stream);
+/* model_engine(batch_x) (train.py:107) up to the per-tile parts of the logits: hT[n, b] = bf16(relu(x_q[b,:] . W1_q[n,:] + b1[n]))
+ * and, in `scratch` (b200ds_fh_forward_scratch_bytes), zpart[n / 128][b] = sum over the 128 units of the tile of W2[n] hT[n, b];
+ * b200ds_fh_logits adds the parts up in tile order (+ b2) -- deterministic, no atomics. */
+B200DS_API size_t b200ds_fh_forward_scratch_bytes(int64_t batch, int n_features, int hidden);
+B200DS_API int b200ds_fh_forward(const void* xq_dev, const void* w1q_dev, const float* params_dev, int64_t batch,
+                                 int n_features, int hidden, void* hT_dev, void* scratch_dev, size_t scratch_bytes,
+                                 uintptr_t stream);
+
+B200DS_API int b200ds_fh_logits(const void* fwd_scratch_dev, const float* params_dev, int64_t batch, int n_features,
+                                int hidden, float* logits_dev, uintptr_t stream);
+/* model_engine.backward(loss) up to the all-reduce (train.py:113) for wide inputs, from dlogits (b200ds_bce_loss_grad):
+ * relu's backward IN PLACE on hT (it becomes the A operand 1[h>0] * bf16(dlogits) of the weight-gradient GEMM -- hT
+ * is consumed), dW2 = sum_b dz h, db1 = W2 * sum_b 1[h>0] dz, db2 = sum_b dz, dW1[n,:] = W2[n] * sum_b A[n,b] x_q[b,:]
+ * (tcgen05 GEMM over the batch, two halves of the batch per output tile meeting through a two-addend
+ * red.global.add: deterministic).  grads_dev (flat layout) is overwritten.  batch % 2048 == 0. */
+B200DS_API size_t b200ds_fh_backward_scratch_bytes(int64_t batch, int n_features, int hidden);
+B200DS_API int b200ds_fh_backward(const void* xq_dev, void* hT_dev, const float* dlogits_dev, const float* params_dev,
+                                  int64_t batch, int n_features, int hidden, float* grads_dev, void* scratch_dev,
+                                  size_t scratch_bytes, uintptr_t stream);
+
 /* ---- end-to-end step with HOST buffers (what bench.py's `e2e` times) ---------------
  * One call = train.py:104-115 for one batch: H2D of x,y from (pinned) host memory,
  * forward, loss, backward, all-reduce, Adam (t = step0 + 1), D2H of the loss, and a
