@@ -31,6 +31,9 @@ WORKLOADS = {
     "wide4096": dict(B=65536, F=20, H=4096),
     "wide8192": dict(B=65536, F=20, H=8192),
     "tiny": dict(B=4, F=20, H=64),
+    # wide inputs ("F = H", SURVEY 8d-4: the extension where layer 1 is a real GEMM); a smaller one for quick runs
+    "wideFH4096": dict(B=65536, F=4096, H=4096),
+    "wideFH1024": dict(B=65536, F=1024, H=1024),
 }
 SEED = 42
 LR = 1e-3
@@ -395,6 +398,81 @@ class WideStep:
         return self.B * (2 * self.F * self.H + 4 * self.H)
 
 
+class WideInputStep:
+    """Device-resident step for the wide-input workloads (F = H): layer 1 as K-loop tcgen05 GEMMs (csrc/mlp_fh.cu).
+    Same surface as WideStep."""
+
+    tc = True
+    fused_update = False
+    p2p = False
+
+    def __init__(self, lib, ctx, dev, wl, world, rank, precision):
+        from b200ds import _lib
+        assert precision == "bf16", "the wide-input path is the bf16 tensor-core path"
+        self.lib, self.ctx, self._lib = lib, ctx, _lib
+        B, F, H = wl["B"], wl["F"], wl["H"]
+        assert lib.b200ds_fh_supported(B, F, H) and lib.b200ds_fh_gen_supported(B, F)
+        self.B, self.F, self.H, self.world = B, F, H, world
+        self.P = F * H + 2 * H + 1
+        self.Ppad = (self.P + 3) // 4 * 4
+        flat = init_flat(F, H)
+        z = lambda n: torch.zeros(n, dtype=torch.float32, device=dev)      # noqa: E731
+        u8 = lambda n: torch.zeros(max(256, n), dtype=torch.uint8, device=dev)      # noqa: E731
+        self.params = z(self.Ppad); self.params[: self.P] = flat.to(dev)
+        self.grads, self.m, self.v = z(self.Ppad), z(self.Ppad), z(self.Ppad)
+        self.y, self.logits, self.dz, self.loss = z(B), z(B), z(B), z(1)
+        self.xq = u8(lib.b200ds_fh_operand_bytes(B, F))
+        self.wq = u8(lib.b200ds_fh_operand_bytes(H, F))
+        self.hT = u8(lib.b200ds_fh_operand_bytes(H, B))
+        self.gen_sc = u8(lib.b200ds_fh_gen_scratch_bytes(B, F))
+        self.fwd_sc = u8(lib.b200ds_fh_forward_scratch_bytes(B, F, H))
+        self.bwd_sc = u8(lib.b200ds_fh_backward_scratch_bytes(B, F, H))
+        self.bce_sc = u8(lib.b200ds_bce_scratch_bytes(B))
+        self.counter = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.seed = SEED + 1000003 * rank
+        self.primed = False
+        self.dominant = dict(name="fh_fwd_kernel (layer-1 GEMM + fused epilogue)", bound="tensor")
+
+    launches = 11      # gen, labels, forward, logits, loss, relu backward, finish, (memset,) wgrad, adam, pack
+
+    def dominant_flops(self):
+        return 2 * self.B * self.F * self.H
+
+    def gen_next(self, st):
+        self._lib.check(self.lib.b200ds_fh_gen_batch_counted(self.xq.data_ptr(), self.y.data_ptr(), self.B, self.F, self.seed, 0,
+                                                             self.counter.data_ptr(), self.gen_sc.data_ptr(), self.gen_sc.numel(), st))
+
+    def pack(self, st):
+        self._lib.check(self.lib.b200ds_fh_pack_bf16(self.params.data_ptr(), self.H, self.F, self.wq.data_ptr(), st))
+
+    def step(self, st, ev_pair=None):
+        lib, chk = self.lib, self._lib.check
+        B, F, H = self.B, self.F, self.H
+        if not self.primed:
+            self.gen_next(st)
+            self.pack(st)
+            self.primed = True
+        if ev_pair:
+            ev_pair[0].record()
+        chk(lib.b200ds_fh_forward(self.xq.data_ptr(), self.wq.data_ptr(), self.params.data_ptr(), B, F, H, self.hT.data_ptr(),
+                                  self.fwd_sc.data_ptr(), self.fwd_sc.numel(), st))
+        if ev_pair:
+            ev_pair[1].record()
+        chk(lib.b200ds_fh_logits(self.fwd_sc.data_ptr(), self.params.data_ptr(), B, F, H, self.logits.data_ptr(), st))
+        chk(lib.b200ds_bce_loss_grad(self.logits.data_ptr(), self.y.data_ptr(), B, self.loss.data_ptr(), self.dz.data_ptr(),
+                                     self.counter.data_ptr(), self.bce_sc.data_ptr(), self.bce_sc.numel(), st))
+        chk(lib.b200ds_fh_backward(self.xq.data_ptr(), self.hT.data_ptr(), self.dz.data_ptr(), self.params.data_ptr(), B, F, H,
+                                   self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
+        # the 4 P-byte gradient bucket crosses NVLink (NCCL, side stream) while the next batch is drawn: the generator is
+        # pure arithmetic, the all-reduce pure data movement
+        chk(lib.b200ds_allreduce_bucket_begin(self.ctx, self.grads.data_ptr(), self.P, st))
+        self.gen_next(st)
+        chk(lib.b200ds_allreduce_bucket_end(self.ctx, st))
+        chk(lib.b200ds_adam_step_counted(self.params.data_ptr(), self.grads.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
+                                         self.Ppad, LR, 0.9, 0.999, 1e-8, self.counter.data_ptr(), 1.0 / self.world, 0, st))
+        self.pack(st)
+
+
 def run_ours(a):
     import torch.distributed as dist
 
@@ -410,7 +488,8 @@ def run_ours(a):
     wl = WORKLOADS[a.workload]
     precision = a.precision
     if precision == "auto":
-        precision = "bf16" if (a.workload != "tiny" and lib.b200ds_tc_supported(wl["B"], wl["F"], wl["H"])) else "fp32"
+        precision = "bf16" if (a.workload != "tiny" and (lib.b200ds_tc_supported(wl["B"], wl["F"], wl["H"]) or
+                                                          lib.b200ds_fh_supported(wl["B"], wl["F"], wl["H"]))) else "fp32"
     ctx = C.c_void_p()
     nid = comm.exchange_nccl_id(lambda: _nccl_id(lib), le)
     idbuf = C.create_string_buffer(nid, 128) if nid else None
@@ -428,7 +507,8 @@ def run_ours(a):
         res = bench_tiny(lib, ctx, dev, world, rank, a, barrier)
         out.update(res)
     else:
-        ws = WideStep(lib, ctx, dev, wl, world, rank, precision)
+        wide_inputs = a.workload.startswith("wideFH")
+        ws = (WideInputStep if wide_inputs else WideStep)(lib, ctx, dev, wl, world, rank, precision)
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
         W = max(3, a.warmup)
         for _ in range(W):
@@ -451,7 +531,7 @@ def run_ours(a):
         clk = ClockSampler(local)
         if rank == 0:             # one sampler per job (NVML queries from 8 processes at once stall the launch threads);
             clk.start()           # it watches the identical load of the warm-up replays and the timed region
-        for _ in range(4000 if wl["H"] <= 4096 else 2000):
+        for _ in range(60 if wide_inputs else (4000 if wl["H"] <= 4096 else 2000)):
             graph.replay()
         barrier()
         trace("clock warm-up replays done")
@@ -616,18 +696,19 @@ def bench_e2e(lib, ctx, dev, wl, world, a, barrier, precision):
     grads, m, v, xs, ys, lg, dl, ls = z(Ppad), z(Ppad), z(Ppad), z(2 * B * F), z(2 * B), z(B), z(B), z(1)   # staging: two batches
     sc = torch.zeros(max(256, lib.b200ds_train_step_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
     tc = precision == "bf16"
-    xq = torch.empty(lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=dev) if tc else None
-    wq = torch.empty(lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=dev) if tc else None
+    fh = tc and bool(lib.b200ds_fh_supported(B, F, H))
+    xq = torch.empty(lib.b200ds_fh_operand_bytes(B, F) if fh else lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=dev) if tc else None
+    wq = torch.empty(lib.b200ds_fh_operand_bytes(H, F) if fh else lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=dev) if tc else None
     bufs = _lib.StepBufs(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), xs.data_ptr(), ys.data_ptr(),
                          lg.data_ptr(), dl.data_ptr(), ls.data_ptr(), sc.data_ptr(), sc.numel(),
                          xq.data_ptr() if tc else None, wq.data_ptr() if tc else None)
-    nbuf = 4
+    nbuf = 2 if fh else 4                    # wide inputs: 1 GiB of pinned host memory per batch
     xh = [torch.randn(B, F).pin_memory() for _ in range(nbuf)]
     yh = [label_rule(x).contiguous().pin_memory() for x in xh]
     lh = torch.zeros(1).pin_memory()
     st = torch.cuda.current_stream().cuda_stream
     step = 0
-    K = max(3, min(a.steps, 20))
+    K = max(3, min(a.steps, 8 if fh else 20))
     def host_step(i):
         # batch i from pinned host memory; batch i+1 announced so that its copy runs behind this step's kernels
         j, jn = i % nbuf, (i + 1) % nbuf

@@ -95,6 +95,10 @@ PROTOTYPES = {
     "b200ds_fh_pack_bf16": (C.c_int, [c_ptr, c_i64, c_i64, c_ptr, c_stream]),
     "b200ds_fh_forward_scratch_bytes": (C.c_size_t, [c_i64, C.c_int, C.c_int]),
     "b200ds_fh_forward": (C.c_int, [c_ptr, c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_ptr, C.c_size_t, c_stream]),
+    "b200ds_fh_gen_supported": (C.c_int, [c_i64, C.c_int]),
+    "b200ds_fh_gen_scratch_bytes": (C.c_size_t, [c_i64, C.c_int]),
+    "b200ds_fh_gen_batch": (C.c_int, [c_ptr, c_ptr, c_i64, C.c_int, c_u64, c_u64, C.POINTER(c_u64), c_ptr, C.c_size_t, c_stream]),
+    "b200ds_fh_gen_batch_counted": (C.c_int, [c_ptr, c_ptr, c_i64, C.c_int, c_u64, c_u64, c_ptr, c_ptr, C.c_size_t, c_stream]),
     "b200ds_fh_logits": (C.c_int, [c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_stream]),
     "b200ds_fh_backward_scratch_bytes": (C.c_size_t, [c_i64, C.c_int, C.c_int]),
     "b200ds_fh_backward": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, C.c_int, C.c_int, c_ptr, c_ptr, C.c_size_t, c_stream]),

@@ -15,6 +15,9 @@ extern "C" {
 size_t b200ds_train_step_scratch_bytes(int64_t batch, int n_features, int hidden) {
   size_t f32 = b200ds_mlp_backward_f32_scratch_bytes(batch, n_features, hidden);
   size_t tcb = b200ds_mlp_backward_tc_scratch_bytes(batch, n_features, hidden);
+  if (b200ds_fh_supported(batch, n_features, hidden))      // wide inputs: [ loss | forward parts | backward parts | hT ]
+    return align_up(b200ds_bce_scratch_bytes(batch), 256) + align_up(b200ds_fh_forward_scratch_bytes(batch, n_features, hidden), 256) +
+           align_up(b200ds_fh_backward_scratch_bytes(batch, n_features, hidden), 256) + align_up(b200ds_fh_operand_bytes(hidden, batch), 256);
   // [ loss scratch | backward scratch (fp32 or tensor-core) | forward slice parts + tile tickets (tensor-core, H > 2048) ]
   return align_up(b200ds_bce_scratch_bytes(batch), 256) + align_up(f32 > tcb ? f32 : tcb, 256) +
          align_up(b200ds_mlp_forward_tc_scratch_bytes(batch, n_features, hidden), 256);
@@ -48,6 +51,22 @@ static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const flo
   B200_REQUIRE(b->scratch && b->scratch_bytes >= need, "train_step_host: scratch too small (%zu < %zu)", b->scratch_bytes, need);
   char* sc = reinterpret_cast<char*>(b->scratch);
   size_t bce_bytes = align_up(b200ds_bce_scratch_bytes(batch), 256);
+  if (b->xq && b->wq && b200ds_fh_supported(batch, n_features, hidden)) {
+    // wide inputs (F = H): pack, layer-1 GEMM, logits, loss, backward (relu, dW2/db1/db2, weight-gradient GEMM)
+    const size_t fwd_b = align_up(b200ds_fh_forward_scratch_bytes(batch, n_features, hidden), 256);
+    const size_t bwd_b = align_up(b200ds_fh_backward_scratch_bytes(batch, n_features, hidden), 256);
+    char* fwd_sc = sc + bce_bytes; char* bwd_sc = fwd_sc + fwd_b; char* hT = bwd_sc + bwd_b;
+    if ((rc = b200ds_fh_pack_bf16(x_dev, batch, n_features, b->xq, stream))) return rc;
+    if ((rc = b200ds_fh_pack_bf16(b->params, hidden, n_features, b->wq, stream))) return rc;
+    if ((rc = b200ds_fh_forward(b->xq, b->wq, b->params, batch, n_features, hidden, hT, fwd_sc, fwd_b, stream))) return rc;
+    if ((rc = b200ds_fh_logits(fwd_sc, b->params, batch, n_features, hidden, b->logits, stream))) return rc;
+    if ((rc = b200ds_bce_loss_grad(b->logits, y_dev, batch, b->loss, b->dlogits, nullptr, sc, bce_bytes, stream))) return rc;
+    if ((rc = b200ds_fh_backward(b->xq, hT, b->dlogits, b->params, batch, n_features, hidden, b->grads, bwd_sc, bwd_b, stream))) return rc;
+    if ((rc = b200ds_allreduce_bucket(ctx, b->grads, P, stream))) return rc;
+    if (step_counter)
+      return b200ds_adam_step_counted(b->params, b->grads, b->exp_avg, b->exp_avg_sq, Ppad, lr, beta1, beta2, eps, step_counter, scale, 0, stream);
+    return b200ds_adam_step(b->params, b->grads, b->exp_avg, b->exp_avg_sq, Ppad, lr, beta1, beta2, eps, step0 + 1, scale, 0, stream);
+  }
   const bool use_tc = b->xq && b->wq && b200ds_tc_supported(batch, n_features, hidden);
   if (use_tc) {
     if ((rc = b200ds_pack_x_bf16(x_dev, batch, n_features, b->xq, stream))) return rc;

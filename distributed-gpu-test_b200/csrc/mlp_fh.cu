@@ -23,6 +23,7 @@
 #include "tc_common.cuh"
 #include <cuda.h>
 #include <cudaTypedefs.h>
+#include "philox.cuh"
 
 namespace b200ds {
 using namespace tc;
@@ -209,6 +210,70 @@ fh_fwd_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc<512>(tmem);
+}
+
+// ---------------------------------------------------------------- generated batch, straight into layout L
+// Element li = row*F + k of torch.randn(B*F, device='cuda') under (seed, offset) is output j % 4 of Philox call
+// (counter offset/4 + j/4, subsequence sub), li = sub + nthreads*j (philox.cu, ATen's mapping).  When F divides nthreads
+// (powers of two up to 8192: nthreads = 303104 = 2^13 * 37 for large batches) a subsequence stays in one COLUMN,
+// k = sub % F, and walks down the rows r0 + (nthreads/F) * j, r0 = sub / F.  A CTA owns 8 consecutive r0 x 32
+// consecutive k (warp = one r0): per Philox call every thread gets four values for four rows, eight lanes pack their
+// eight neighbouring columns into one 16-byte store, and the CTA's eight warps fill whole 32-byte sectors of the core
+// matrices (their eight rows are consecutive).  All four outputs of every Philox call are used; fp32 x is never stored.
+// Labels (train.py:22-23) need sum_{k < F/2} x[row, k]: a warp's 32 columns are summed by shuffles and stored as
+// ypart[row][k / 32]; fh_label_kernel adds a row's parts up in column order (deterministic) and thresholds.
+__device__ __forceinline__ void fh_normals4(uint64_t ctr, uint64_t sub, uint2 key, float (&out)[4]) {
+  const uint4 r = philox4x32_10(make_uint4((unsigned)ctr, (unsigned)(ctr >> 32), (unsigned)sub, (unsigned)(sub >> 32)), key);
+  const float2 p = box_muller(r.x, r.y), q = box_muller(r.z, r.w);
+  out[0] = normal_transform(p.x); out[1] = normal_transform(p.y);
+  out[2] = normal_transform(q.x); out[3] = normal_transform(q.y);
+}
+
+__global__ void __launch_bounds__(256)
+fh_gen_kernel(unsigned char* __restrict__ xq, float* __restrict__ ypart, int64_t batch, int F, uint2 key, uint64_t ctr0,
+              uint32_t nthreads, int calls, int calls_per_cta, const unsigned long long* __restrict__ draw_counter) {
+  if (draw_counter) ctr0 += (uint64_t)(*draw_counter) * (uint64_t)calls;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rstride = (int)(nthreads / (uint32_t)F);                    // rows between consecutive outputs of a subsequence
+  const int r0 = blockIdx.y * 8 + warp;
+  if (r0 >= rstride) return;
+  const int k = blockIdx.x * 32 + lane;
+  const uint64_t sub = (uint64_t)r0 * (uint64_t)F + (uint64_t)k;
+  const int half_blocks = F / 64;                                       // 32-column blocks inside the first half of a row
+  const int c_begin = blockIdx.z * calls_per_cta, c_end = min(calls, c_begin + calls_per_cta);
+  for (int c = c_begin; c < c_end; ++c) {
+    const int64_t row_c = (int64_t)r0 + (int64_t)rstride * 4 * c;       // row of output 0
+    if (row_c >= batch) break;
+    float v[4];
+    fh_normals4(ctr0 + (uint64_t)c, sub, key, v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t row = row_c + (int64_t)rstride * i;
+      if (row >= batch) break;                                          // warp-uniform
+      // eight lanes' bf16 values -> one 16-byte store
+      const uint32_t h16 = (uint32_t)__bfloat16_as_ushort(__float2bfloat16(v[i]));
+      const uint32_t pair = h16 | (__shfl_down_sync(0xffffffffu, h16, 1) << 16);
+      const uint32_t pair2 = __shfl_down_sync(0xffffffffu, pair, 2);
+      const uint32_t q2 = __shfl_down_sync(0xffffffffu, pair, 4), q3 = __shfl_down_sync(0xffffffffu, pair2, 4);
+      if ((lane & 7) == 0) *reinterpret_cast<uint4*>(xq + fh_byte(row, k, F)) = make_uint4(pair, pair2, q2, q3);
+      if ((int)blockIdx.x < half_blocks) {                              // this block of 32 columns lies in the first half of the row
+        float a = v[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        if (lane == 0) ypart[(size_t)row * half_blocks + blockIdx.x] = a;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+fh_label_kernel(const float* __restrict__ ypart, int64_t batch, int half_blocks, float* __restrict__ y) {
+  const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= batch) return;
+  const float* p = ypart + (size_t)row * half_blocks;
+  float a = 0.f;
+  for (int j = 0; j < half_blocks; ++j) a += p[j];
+  y[row] = a > 0.f ? 1.f : 0.f;
 }
 
 // ---------------------------------------------------------------- logits from the forward's parts
@@ -484,6 +549,61 @@ int b200ds_fh_forward(const void* xq_dev, const void* w1q_dev, const float* para
                                                                reinterpret_cast<float*>(scratch_dev), batch, n_features, hidden);
   B200_LAUNCH_CHECK();
   return B200DS_OK;
+}
+
+size_t b200ds_fh_gen_scratch_bytes(int64_t batch, int n_features) {
+  return batch > 0 && n_features >= 64 ? (size_t)batch * (size_t)(n_features / 64) * sizeof(float) : 0;
+}
+
+int b200ds_fh_gen_supported(int64_t batch, int n_features) {
+  if (batch <= 0 || batch % 8 != 0 || n_features < 64 || n_features % 64 != 0) return 0;
+  int grid, calls;
+  philox_plan(batch * n_features, &grid, &calls);
+  return ((int64_t)grid * 256) % n_features == 0 ? 1 : 0;
+}
+
+static int fh_launch_gen(void* xq_dev, float* y_dev, int64_t batch, int n_features, uint64_t seed, uint64_t offset,
+                         const uint64_t* draw_counter_dev, uint64_t* offset_advance, void* scratch_dev, size_t scratch_bytes,
+                         uintptr_t stream) {
+  B200_REQUIRE(b200ds_fh_gen_supported(batch, n_features),
+               "fh_gen_batch: n_features must divide the generator's thread count (a power of two in [64, 8192] for large batches) and "
+               "batch %% 8 == 0 (got B=%lld F=%d); otherwise use b200ds_philox_normal + b200ds_fh_pack_bf16", (long long)batch, n_features);
+  B200_REQUIRE(offset % 4 == 0, "fh_gen_batch: offset must be a multiple of 4");
+  B200_REQUIRE(xq_dev && y_dev, "fh_gen_batch: null pointer");
+  const size_t need = b200ds_fh_gen_scratch_bytes(batch, n_features);
+  B200_REQUIRE(scratch_dev && scratch_bytes >= need, "fh_gen_batch: scratch too small (%zu < %zu)", scratch_bytes, need);
+  int grid, calls;
+  philox_plan(batch * n_features, &grid, &calls);
+  const uint32_t nthreads = (uint32_t)grid * 256u;
+  const int rstride = (int)(nthreads / (uint32_t)n_features);
+  // enough CTAs for ~8 waves of the machine: the call range is cut into pieces
+  const int ctas_xy = (n_features / 32) * ((rstride + 7) / 8);
+  int pieces = (sm_count() * 8 * 8 + ctas_xy - 1) / ctas_xy;
+  if (pieces < 1) pieces = 1;
+  if (pieces > calls) pieces = calls;
+  const int per = (calls + pieces - 1) / pieces;
+  pieces = (calls + per - 1) / per;
+  cudaStream_t st = as_stream(stream);
+  fh_gen_kernel<<<dim3(n_features / 32, (rstride + 7) / 8, pieces), 256, 0, st>>>(
+      reinterpret_cast<unsigned char*>(xq_dev), reinterpret_cast<float*>(scratch_dev), batch, n_features,
+      make_uint2((unsigned)seed, (unsigned)(seed >> 32)), offset / 4, nthreads, calls, per,
+      reinterpret_cast<const unsigned long long*>(draw_counter_dev));
+  B200_LAUNCH_CHECK();
+  fh_label_kernel<<<(unsigned)((batch + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float*>(scratch_dev), batch, n_features / 64, y_dev);
+  B200_LAUNCH_CHECK();
+  if (offset_advance) *offset_advance = (uint64_t)calls * 4;
+  return B200DS_OK;
+}
+
+int b200ds_fh_gen_batch(void* xq_dev, float* y_dev, int64_t batch, int n_features, uint64_t seed, uint64_t offset,
+                        uint64_t* offset_advance, void* scratch_dev, size_t scratch_bytes, uintptr_t stream) {
+  return fh_launch_gen(xq_dev, y_dev, batch, n_features, seed, offset, nullptr, offset_advance, scratch_dev, scratch_bytes, stream);
+}
+
+int b200ds_fh_gen_batch_counted(void* xq_dev, float* y_dev, int64_t batch, int n_features, uint64_t seed, uint64_t offset0,
+                                const uint64_t* draw_counter_dev, void* scratch_dev, size_t scratch_bytes, uintptr_t stream) {
+  B200_REQUIRE(draw_counter_dev != nullptr, "fh_gen_batch_counted: null draw counter");
+  return fh_launch_gen(xq_dev, y_dev, batch, n_features, seed, offset0, draw_counter_dev, nullptr, scratch_dev, scratch_bytes, stream);
 }
 
 int b200ds_fh_logits(const void* fwd_scratch_dev, const float* params_dev, int64_t batch, int n_features, int hidden,

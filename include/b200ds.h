@@ -329,6 +329,19 @@ B200DS_API int b200ds_fh_forward(const void* xq_dev, const void* w1q_dev, const 
                                  int n_features, int hidden, void* hT_dev, void* scratch_dev, size_t scratch_bytes,
                                  uintptr_t stream);
 
+/* make_synthetic_data (train.py:19-24) for generated batches of wide inputs: xq (layout L) = bf16 of
+ * torch.randn(batch*F, device='cuda') under (seed, offset) viewed as [batch, F], y[b] = 1[sum_{k < F/2} x[b,k] > 0]
+ * on the fp32 values (32-column partial sums by shuffle, added in column order: deterministic).  Needs F to divide
+ * the generator's thread count (b200ds_fh_gen_supported; powers of two in [64, 8192] for large batches);
+ * scratch: b200ds_fh_gen_scratch_bytes.  The _counted form takes the draw index from a device counter. */
+B200DS_API int b200ds_fh_gen_supported(int64_t batch, int n_features);
+B200DS_API size_t b200ds_fh_gen_scratch_bytes(int64_t batch, int n_features);
+B200DS_API int b200ds_fh_gen_batch(void* xq_dev, float* y_dev, int64_t batch, int n_features, uint64_t seed,
+                                   uint64_t offset, uint64_t* offset_advance, void* scratch_dev, size_t scratch_bytes,
+                                   uintptr_t stream);
+B200DS_API int b200ds_fh_gen_batch_counted(void* xq_dev, float* y_dev, int64_t batch, int n_features, uint64_t seed,
+                                           uint64_t offset0, const uint64_t* draw_counter_dev, void* scratch_dev,
+                                           size_t scratch_bytes, uintptr_t stream);
 B200DS_API int b200ds_fh_logits(const void* fwd_scratch_dev, const float* params_dev, int64_t batch, int n_features,
                                 int hidden, float* logits_dev, uintptr_t stream);
 /* model_engine.backward(loss) up to the all-reduce (train.py:113) for wide inputs, from dlogits (b200ds_bce_loss_grad):
@@ -350,7 +363,8 @@ B200DS_API int b200ds_fh_backward(const void* xq_dev, void* hT_dev, const float*
  * kernels when `xq` and `wq` are supplied (non-NULL); everything else the per-stage fp32
  * kernels.  The caller supplies every device buffer in `bufs` (all borrowed):
  *   scratch: b200ds_train_step_scratch_bytes(...) bytes, zeroed once by the caller;
- *   xq / wq: b200ds_tc_xq_bytes(batch) / b200ds_tc_wq_bytes(H) bytes, or NULL for fp32.
+ *   xq / wq: b200ds_tc_xq_bytes(batch) / b200ds_tc_wq_bytes(H) bytes, or NULL for fp32; for shapes of the
+ *            wide-input class (b200ds_fh_supported) b200ds_fh_operand_bytes(batch, F) / (H, F) bytes.
  * With more than one rank the exchange is ncclAllReduce + the Adam kernel, or the single
  * peer-memory kernel when b200ds_ctx_enable_p2p has been called with room for the bucket. */
 typedef struct b200ds_step_bufs {

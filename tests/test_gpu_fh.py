@@ -120,3 +120,110 @@ def test_fh_backward_vs_fp64(lib, cuda_dev, B, F, H):
         scale = torch.cat([s_w1.reshape(-1), s_b1, s_w2, dzd.abs().sum().reshape(1)])
         bad = (g - ref).abs() > 2e-5 * scale + 1e-30                             # fp32 sums of exactly these terms
         assert not bool(bad.any()), (rep, int(bad.sum()), int(bad.nonzero()[0]), float((g - ref).abs().max()))
+
+
+@pytest.mark.parametrize("B,F", [(2048, 256), (4096, 1024), (8192, 4096), (512, 512), (65536, 4096)])
+def test_fh_generator_is_torch_randn_bit_for_bit(lib, cuda_dev, B, F):
+    """b200ds_fh_gen_batch == bf16 pack of torch.randn(B*F, device='cuda') under the same seed / offset, three consecutive
+    draws (the third through the device draw counter); labels = sign of the fp64 row sums of the fp32 values wherever that
+    sum is not within rounding of zero."""
+    import ctypes as C
+    assert lib.b200ds_fh_gen_supported(B, F) == 1
+    seed = 1234 + B + F
+    g = torch.Generator(device=cuda_dev); g.manual_seed(seed)
+    xq = torch.empty(lib.b200ds_fh_operand_bytes(B, F), dtype=torch.uint8, device=cuda_dev)
+    xq_ref = torch.empty_like(xq)
+    y = torch.empty(B, device=cuda_dev)
+    sc = torch.zeros(lib.b200ds_fh_gen_scratch_bytes(B, F), dtype=torch.uint8, device=cuda_dev)
+    ctr = torch.zeros(1, dtype=torch.int64, device=cuda_dev)
+    off = 0
+    for draw in range(3):
+        x = torch.randn(B * F, device=cuda_dev, generator=g)
+        _chk(lib.b200ds_fh_pack_bf16(x.data_ptr(), B, F, xq_ref.data_ptr(), _st()))
+        xq.zero_(); y.fill_(-1)
+        adv = C.c_uint64(0)
+        if draw < 2:
+            _chk(lib.b200ds_fh_gen_batch(xq.data_ptr(), y.data_ptr(), B, F, seed, off, C.byref(adv), sc.data_ptr(), sc.numel(), _st()))
+            off += adv.value
+        else:
+            ctr.fill_(draw)
+            _chk(lib.b200ds_fh_gen_batch_counted(xq.data_ptr(), y.data_ptr(), B, F, seed, 0, ctr.data_ptr(), sc.data_ptr(), sc.numel(), _st()))
+        torch.cuda.synchronize()
+        assert torch.equal(xq, xq_ref), (B, F, draw)
+        s64 = x.view(B, F)[:, : F // 2].double().sum(dim=1)
+        clear = s64.abs() > 1e-3
+        assert torch.equal(y[clear], (s64[clear] > 0).float()), (B, F, draw)
+        assert bool(((y == 0) | (y == 1)).all())
+    assert lib.b200ds_fh_gen_supported(2048, 768) == 0        # 768 does not divide the generator's 303104 threads
+
+
+def test_fh_n_steps_track_fp32_autograd(lib, cuda_dev):
+    """The wide-input step as bench.py runs it (generator -> GEMM forward -> logits -> loss -> backward -> Adam -> pack, device
+    counters), 10 steps eagerly and 10 steps as a replayed CUDA graph: same bits; and against torch's own fp32 modules
+    (nn.Linear / ReLU / BCEWithLogitsLoss / autograd / optim.Adam, the objects train.py builds) on the same batches: every
+    step's loss within 2e-2; parameters after the 10 steps: each group (W1, b1, W2, b2) within 2e-2 of the fp32 group in
+    norm (north_star's bf16 tolerance), no element further away than Adam's reach n * lr, and the step each group took
+    within 1e-1 of fp32's.  (The step is the looser figure on purpose: bf16 layer-1 operands flip the relu of the
+    ~0.3 % of (sample, unit) pairs whose pre-activation is within rounding of zero, which perturbs a W1 gradient -- a
+    random-sign sum over the batch -- by ~sqrt(0.003) = 5 %, and Adam turns a gradient into a step of fixed size.)"""
+    import ctypes as C
+
+    import bench
+    from b200ds import _lib
+    wl = dict(B=4096, F=1024, H=512)
+    B, F, H = wl["B"], wl["F"], wl["H"]
+    n = 10
+
+    def run(graph):
+        ctx = C.c_void_p()
+        _lib.check(lib.b200ds_ctx_create(0, 0, 1, None, C.byref(ctx)))
+        ws = bench.WideInputStep(lib, ctx, cuda_dev, wl, 1, 0, "bf16")
+        losses, ys = [], []
+        ws.step(_st()); torch.cuda.synchronize(); losses.append(float(ws.loss)); ys.append(None)
+        g = None
+        if graph:
+            g = torch.cuda.CUDAGraph()
+            cap = torch.cuda.Stream(device=cuda_dev)
+            cap.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.graph(g, stream=cap):
+                ws.step(torch.cuda.current_stream().cuda_stream)
+            torch.cuda.current_stream().wait_stream(cap)
+        for k in range(1, n):
+            ys.append(ws.y.clone())
+            g.replay() if graph else ws.step(_st())
+            torch.cuda.synchronize()
+            losses.append(float(ws.loss))
+        if g is not None:
+            g.reset()
+        out = (losses, ys, ws.params[: ws.P].clone(), ws.seed)
+        _lib.check(lib.b200ds_ctx_destroy(ctx))
+        return out
+
+    l_e, ys, p_e, seed = run(False)
+    l_g, _, p_g, _ = run(True)
+    assert l_e == l_g and torch.equal(p_e, p_g)
+    # torch fp32 on the same batches
+    flat0 = bench.init_flat(F, H).to(cuda_dev)
+    net = torch.nn.Sequential(torch.nn.Linear(F, H), torch.nn.ReLU(), torch.nn.Linear(H, 1)).to(cuda_dev)
+    with torch.no_grad():
+        net[0].weight.copy_(flat0[: H * F].view(H, F)); net[0].bias.copy_(flat0[H * F: H * F + H])
+        net[2].weight.copy_(flat0[H * F + H: H * F + 2 * H].view(1, H)); net[2].bias.copy_(flat0[H * F + 2 * H:])
+    opt = torch.optim.Adam(net.parameters(), lr=bench.LR)
+    crit = torch.nn.BCEWithLogitsLoss()
+    gen = torch.Generator(device=cuda_dev); gen.manual_seed(seed)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    for k in range(n):
+        x = torch.randn(B * F, device=cuda_dev, generator=gen).view(B, F)
+        y = (x[:, : F // 2].double().sum(dim=1) > 0).float() if ys[k] is None else ys[k]
+        loss = crit(net(x), y.view(B, 1))
+        opt.zero_grad(set_to_none=True)
+        loss.backward()
+        opt.step()
+        assert abs(l_e[k] - float(loss.detach())) <= 2e-2 * abs(float(loss.detach())), (k, l_e[k], float(loss.detach()))
+    ref = torch.cat([t.detach().reshape(-1) for t in (net[0].weight, net[0].bias, net[2].weight, net[2].bias)])
+    d = (p_e.double() - ref.double()).abs()
+    assert float(d.max()) <= n * bench.LR, float(d.max())
+    for name, o, cnt in (("w1", 0, H * F), ("b1", H * F, H), ("w2", H * F + H, H), ("b2", H * F + 2 * H, 1)):
+        a, r, z0 = p_e[o:o + cnt].double(), ref[o:o + cnt].double(), flat0[o:o + cnt].double()
+        assert float((a - r).norm()) <= 2e-2 * float(r.norm()), (name, float((a - r).norm() / r.norm()))
+        assert float((a - r).norm()) <= 1e-1 * float((r - z0).norm()), (name, float((a - r).norm() / (r - z0).norm()))
