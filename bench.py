@@ -63,6 +63,21 @@ def peaks():
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sus=1400.0, src="fallback")   # B200_PROFILING.md fallback
 
 
+def profiled_traffic(workload, precision):
+    """DRAM bytes per launch of the dominant kernel (dram__bytes_read.sum + dram__bytes_write.sum) from the committed
+    `ncu --set full` capture, profiles/ncu_traffic.json -- only for a workload that was profiled, and only while the
+    kernel's source file is still the one that was profiled (sha-256 of the file); otherwise None."""
+    import hashlib
+    try:
+        ent = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(workload)
+        if not ent or ent.get("dtype") != ("bf16" if precision == "bf16" else "f32"):
+            return None
+        sha = hashlib.sha256(open(os.path.join(ROOT, ent["source"]), "rb").read()).hexdigest()[:16]
+        return ent["traffic_bytes"] if sha == ent["source_sha16"] else None
+    except Exception:       # noqa: BLE001
+        return None
+
+
 def trace(msg):
     if os.environ.get("B200DS_BENCH_TRACE"):
         sys.stderr.write(f"[bench rank {os.environ.get('RANK', 0)}] {msg}\n")
@@ -531,7 +546,8 @@ def run_ours(a):
         clk = ClockSampler(local)
         if rank == 0:             # one sampler per job (NVML queries from 8 processes at once stall the launch threads);
             clk.start()           # it watches the identical load of the warm-up replays and the timed region
-        for _ in range(60 if wide_inputs else (4000 if wl["H"] <= 4096 else 2000)):
+        settle = int(os.environ.get("B200DS_BENCH_SETTLE", 60 if wide_inputs else (4000 if wl["H"] <= 4096 else 2000)))   # profiling runs shorten it
+        for _ in range(settle):
             graph.replay()
         barrier()
         trace("clock warm-up replays done")
@@ -567,10 +583,7 @@ def run_ours(a):
         value = world * wl["B"] * K / (dev_ms / 1e3)
         loss_last = float(ws.loss)
         achieved = ws.dominant_flops() / (k_ms / 1e3) / 1e12
-        # DRAM bytes per launch of that kernel from the committed `ncu --set full` capture
-        # (profiles/r01_ncu_full_tc_kernels_v3.txt: dram__bytes_read.sum + dram__bytes_write.sum); only known
-        # for the configuration that was profiled
-        traffic = 5016576 if (a.workload == "wide4096" and precision == "bf16") else None
+        traffic = profiled_traffic(a.workload, precision)
         roof = dict(bound="tensor", achieved=achieved, peak=pk["tf_sus"], unit="TFLOP/s", frac=achieved / pk["tf_sus"],
                     traffic=traffic, kernel=ws.dominant["name"], kernel_ms=k_ms, peak_source=f"{pk['src']} bf16 sustained",
                     step_frac=step_flops(**wl) / (ms_per_step / 1e3) / 1e12 / pk["tf_sus"],
