@@ -595,6 +595,7 @@ def run_ours(a):
         if world > 1:
             out["xrank"] = cross_rank_checks(ws, st, dev, world)
             trace("cross-rank checks done")
+            out["allreduce"] = bucket_allreduce_rate(lib, ctx, ws, st, dev, world)
         e2e = bench_e2e(lib, ctx, dev, wl, world, a, barrier, precision)
         trace("e2e done")
         out.update(dict(value=value, ms_per_step=ms_per_step, roofline=roof, e2e=e2e, clocks=clk.summary(),
@@ -633,6 +634,31 @@ def run_ours(a):
             dist.destroy_process_group()
         except Exception:       # noqa: BLE001
             pass
+
+
+def bucket_allreduce_rate(lib, ctx, ws, st, dev, world):
+    """The step's gradient bucket (4 P bytes) through ncclAllReduce alone, outside the timed region: bus GB/s against
+    NVLink 5's 900 GB/s per direction per GPU (north_star: "allreduce bus GB/s is reported against NVLink peak")."""
+    import torch.distributed as dist
+    from b200ds import _lib
+    buf = torch.ones(ws.Ppad, dtype=torch.float32, device=dev)
+    n = ws.P
+    for _ in range(3):
+        _lib.check(lib.b200ds_allreduce_bucket(ctx, buf.data_ptr(), n, st))
+    dist.barrier(); torch.cuda.synchronize()
+    iters = 20
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        _lib.check(lib.b200ds_allreduce_bucket(ctx, buf.data_ptr(), n, st))
+    e1.record(); torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / iters], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    us = float(t) * 1e3
+    algbw = 4 * n / (us * 1e-6) / 1e9
+    bus = algbw * 2 * (world - 1) / world
+    return dict(bucket_bytes=4 * n, us=round(us, 2), algbw_gbs=round(algbw, 1), busbw_gbs=round(bus, 1), nvlink_nominal_gbs=900,
+                frac_of_nominal=round(bus / 900, 3), note="ncclAllReduce of the flat fp32 gradient bucket, eager back-to-back calls")
 
 
 def cross_rank_checks(ws, st, dev, world):

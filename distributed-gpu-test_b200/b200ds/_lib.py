@@ -55,6 +55,7 @@ PROTOTYPES = {
     "b200ds_allreduce_bucket_end": (C.c_int, [c_ptr, c_stream]),
     "b200ds_zero1_step": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, C.c_double, C.c_double, C.c_double, C.c_double,
                                     c_i64, c_stream]),
+    "b200ds_collective": (C.c_int, [c_ptr, C.c_int, C.c_int, c_ptr, c_i64, c_stream]),
     "b200ds_broadcast_params": (C.c_int, [c_ptr, c_ptr, c_i64, c_stream]),
     "b200ds_barrier": (C.c_int, [c_ptr]),
     "b200ds_adam_step": (C.c_int, [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, C.c_double, C.c_double, C.c_double,

@@ -220,6 +220,35 @@ int b200ds_zero1_step(b200ds_ctx* ctx, float* params_dev, float* grads_dev, floa
   return B200DS_OK;
 }
 
+// One collective of the step's repertoire on a raw buffer, for the fabric sweep (tools/allreduce_sweep.py; BASELINE
+// config 5, SURVEY 8f-4 -- and the reference's own purpose, README.md:3: an acceptance check of NCCL over the fabric).
+int b200ds_collective(b200ds_ctx* ctx, int op, int dtype, void* buf_dev, int64_t n, uintptr_t stream) {
+  B200_REQUIRE(ctx != nullptr, "collective: null context");
+  B200_REQUIRE(op >= 0 && op <= 2, "collective: op must be 0 (all-reduce), 1 (reduce-scatter) or 2 (all-gather)");
+  B200_REQUIRE(dtype == 0 || dtype == 1, "collective: dtype must be 0 (fp32) or 1 (bf16)");
+  B200_REQUIRE(n >= 0, "collective: negative n");
+  if (ctx->world == 1 || n == 0) return B200DS_OK;
+  B200_REQUIRE(buf_dev != nullptr, "collective: null buffer");
+  B200_REQUIRE(op == 0 || n % ctx->world == 0, "collective: n (%lld) must be a multiple of the world size for reduce-scatter / all-gather", (long long)n);
+  if (!ctx->comm) { set_error("collective: context has no communicator"); return B200DS_ERR_STATE; }
+  const NcclApi* api = nccl_api();
+  if (!api) return B200DS_ERR_NCCL;
+  const ncclDataType_t dt = dtype == 0 ? ncclFloat32 : ncclBfloat16;
+  const size_t esz = dtype == 0 ? 4 : 2;
+  const int64_t shard = n / ctx->world;
+  char* base = reinterpret_cast<char*>(buf_dev);
+  char* mine = base + (size_t)shard * ctx->rank * esz;
+  cudaStream_t s = as_stream(stream);
+  B200_CUDA(cudaEventRecord(ctx->ev_ready, s));
+  B200_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_ready, 0));
+  if (op == 0) B200_NCCL(api, api->AllReduce(base, base, (size_t)n, dt, ncclSum, ctx->comm, ctx->side));
+  else if (op == 1) B200_NCCL(api, api->ReduceScatter(base, mine, (size_t)shard, dt, ncclSum, ctx->comm, ctx->side));
+  else B200_NCCL(api, api->AllGather(mine, base, (size_t)shard, dt, ctx->comm, ctx->side));
+  B200_CUDA(cudaEventRecord(ctx->ev_done, ctx->side));
+  B200_CUDA(cudaStreamWaitEvent(s, ctx->ev_done, 0));
+  return B200DS_OK;
+}
+
 int b200ds_broadcast_params(b200ds_ctx* ctx, float* params_dev, int64_t n, uintptr_t stream) {
   B200_REQUIRE(ctx != nullptr, "broadcast_params: null context");
   if (ctx->world == 1 || n <= 0) return B200DS_OK;

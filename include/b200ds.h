@@ -143,6 +143,12 @@ B200DS_API int b200ds_allreduce_bucket_end(b200ds_ctx* ctx, uintptr_t stream);
 B200DS_API int b200ds_zero1_step(b200ds_ctx* ctx, float* params_dev, float* grads_dev, float* exp_avg_shard_dev,
                                  float* exp_avg_sq_shard_dev, int64_t n, double lr, double beta1, double beta2,
                                  double eps, int64_t step, uintptr_t stream);
+/* One NCCL collective on a raw buffer, ordered like b200ds_allreduce_bucket (side stream, event-chained), for the
+ * fabric sweep tool (BASELINE config 5 "allreduce bus GB/s sweep vs bucket size"; the reference's own purpose is
+ * an acceptance check of NCCL over the fabric, README.md:3).  op: 0 all-reduce(sum) in place, 1 reduce-scatter (the
+ * rank's shard of the sum lands at its own offset rank*n/W), 2 all-gather (from that offset into the whole buffer).
+ * dtype: 0 fp32, 1 bf16.  n elements; n % world == 0 for ops 1 and 2. */
+B200DS_API int b200ds_collective(b200ds_ctx* ctx, int op, int dtype, void* buf_dev, int64_t n, uintptr_t stream);
 /* Parameter broadcast from rank 0 done by deepspeed.initialize (train.py:87-93). */
 B200DS_API int b200ds_broadcast_params(b200ds_ctx* ctx, float* params_dev, int64_t n, uintptr_t stream);
 /* dist.barrier() at teardown (train.py:134): host-blocking. */
