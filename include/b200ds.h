@@ -11,10 +11,13 @@
  * Conventions
  *   - every pointer named *_dev / documented "device" is a raw CUDA device pointer
  *     (tensor.data_ptr()); the caller (torch) owns the memory and keeps it alive until
- *     the stream work that uses it has finished.  The library allocates nothing on the
- *     step path; kernels that need scratch take it from the caller
- *     (see the *_scratch_bytes queries).  A context owns only its side stream, events,
- *     pinned mailbox and NCCL communicator.
+ *     the stream work that uses it has finished.  Kernels that need scratch take it from the
+ *     caller (see the *_scratch_bytes queries); the per-kernel entry points allocate nothing.
+ *     A context owns its side stream, events and NCCL communicator; two calls make it own more,
+ *     each on FIRST use only: b200ds_ctx_enable_p2p (the peer-mapped exchange buffer, a flag row,
+ *     a pinned mailbox) and b200ds_train_step_host_prefetch (a copy stream and event, a capture
+ *     stream, one device word and one pinned word, and the CUDA graphs of the step) -- all freed
+ *     by b200ds_ctx_destroy.
  *   - `stream` is a cudaStream_t passed as uintptr_t (0 = legacy default stream).  All
  *     work is stream-ordered; no entry point synchronises the host unless it says so.
  *   - return value: 0 on success, otherwise one of B200DS_ERR_*; b200ds_last_error()
@@ -171,7 +174,7 @@ B200DS_API int b200ds_adam_step_counted(float* params_dev, float* grads_dev, flo
                              int zero_grad, uintptr_t stream);
 
 /* ---- fused tiny-shape step (train.py:104-117 in one launch) ------------------------
- * For the reference's own shape class (F <= 32, H <= 1024, per-step batch <= 32): one CTA
+ * For the reference's own shape class (F <= 32, H <= 256, per-step batch <= 32): one CTA
  * keeps the 1409 parameters and their Adam state in registers and runs `n_steps`
  * consecutive training steps: gather rows order_dev[s*batch .. ) of the resident
  * dataset, forward, loss, backward, and -- when apply_adam != 0 (world == 1) -- the Adam
