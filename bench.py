@@ -350,7 +350,7 @@ class WideStep:
                 chk(fn(self.ctx, self.bwd_sc.data_ptr(), self.bwd_sc.numel(), B, F, H, self.params.data_ptr(),
                        self.grads.data_ptr(), self.m.data_ptr(), self.v.data_ptr(), self.wq.data_ptr(),
                        LR, 0.9, 0.999, 1e-8, 0, self.counter.data_ptr(), self.loss.data_ptr(), stream_handle))
-            if self.world == 1:
+            if self.world == 1:        # (the update beside the generator on a second stream was measured: 99 us against 94)
                 update(lib.b200ds_update_tc, st)
                 self.gen_next(st)
                 return

@@ -614,3 +614,23 @@ def test_engine_rejects_what_is_outside_the_path(cuda_dev):
         engine(torch.zeros(4, 20))                       # host tensor: there is no CPU path
     with pytest.raises(RuntimeError):
         engine.backward(torch.zeros((), device=cuda_dev))
+
+
+def test_sweep_tool_and_collective_entry_point(lib, cuda_dev):
+    """tools/allreduce_sweep.py runs end to end on one rank (every collective is a no-op there) and prints its table;
+    b200ds_collective checks its arguments."""
+    import json
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT")}
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "allreduce_sweep.py"), "--quick"], capture_output=True, text=True,
+                       env=env, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    doc = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    ops = {(row["op"], row["dtype"]) for row in doc["rows"]}
+    assert {("allreduce", "f32"), ("allreduce", "bf16"), ("reduce_scatter", "f32"), ("all_gather", "bf16")} <= ops
+    ctx = C.c_void_p()
+    _check(lib, lib.b200ds_ctx_create(0, 0, 1, None, C.byref(ctx)))
+    buf = torch.ones(64, device=cuda_dev)
+    assert lib.b200ds_collective(ctx, 0, 0, buf.data_ptr(), 64, _st()) == 0          # one rank: nothing to do
+    assert lib.b200ds_collective(ctx, 3, 0, buf.data_ptr(), 64, _st()) == 1          # no such op
+    assert lib.b200ds_collective(ctx, 0, 2, buf.data_ptr(), 64, _st()) == 1          # no such dtype
+    _check(lib, lib.b200ds_ctx_destroy(ctx))

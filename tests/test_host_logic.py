@@ -74,3 +74,25 @@ def test_train_py_fails_loudly_without_gpu():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "train.py"), "--epochs", "1"], capture_output=True, text=True,
                        env={k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")})
     assert r.returncode != 0 and "Epoch" not in r.stdout
+
+
+def test_bench_reference_arm_lines(tmp_path):
+    """`bench.py --impl reference`: one JSON line with the contract's keys; with --gpus 2 rank 0 spawns two gloo
+    processes and the other torchrun ranks print nothing."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT")}
+    for gpus in (1, 2):
+        r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", str(gpus), "--steps", "3",
+                            "--warmup", "1", "--workload", "tiny"], capture_output=True, text=True, env=env, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        line = json.loads(r.stdout.strip().splitlines()[-1])
+        assert line["impl"] == "reference" and line["n_gpus"] == gpus and line["unit"] == "samples/s" and line["value"] > 0
+        assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
+        assert line["config"]["parallelism"] == f"dp{gpus}" and line["steps"] == 3
+    env2 = dict(env, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1")
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "2", "--warmup", "1",
+                        "--workload", "tiny"], capture_output=True, text=True, env=env2, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip() == ""
