@@ -71,12 +71,15 @@ class B200Engine:
         # W1 row, b1 and W2 are zero: they add nothing to the logits, receive zero gradients and stay zero
         # under Adam, so the padded model IS the model.  Batches are padded with rows whose dlogits are zero.
         self.H = self.H_model
+        self._wide = False                    # wide inputs: layer 1 as K-loop GEMMs (b200ds_fh_*)
         if self.cfg["precision"] == "bf16":
             self.H = (self.H_model + 127) // 128 * 128
-            if not self.lib.b200ds_tc_supported(128, self.F, self.H):
+            if self.lib.b200ds_fh_supported(2048, self.F, self.H):
+                self._wide = True
+            elif not self.lib.b200ds_tc_supported(128, self.F, self.H):
                 raise NotImplementedError(
-                    "bf16.enabled: the tensor-core path takes n_features <= 30 (got F=%d, H=%d); there is no silent "
-                    "fp32 substitute -- drop bf16.enabled for this model" % (self.F, self.H_model))
+                    "bf16.enabled: the tensor-core paths take n_features <= 30, or a multiple of 256 (got F=%d, H=%d); there "
+                    "is no silent fp32 substitute -- drop bf16.enabled for this model" % (self.F, self.H_model))
         self.P = self.F * self.H + 2 * self.H + 1
         self.stage = self.cfg["stage"]
         quantum = 4 * self.le.world_size if self.stage == 1 else 4      # stage 1 shards the flat vector W ways
@@ -171,7 +174,34 @@ class B200Engine:
         B = x.shape[0]
         stream = _lib.current_stream()
         self._tc = self.cfg["precision"] == "bf16"
-        if self._tc:
+        if self._tc and self._wide:
+            # wide inputs: pack the batch (padded to the shape class with zero rows, whose dlogits stay zero), layer-1 GEMM
+            # with the fused epilogue, logits from its per-tile parts
+            lib = self.lib
+            Bp = (B + 2047) // 2048 * 2048
+            self._Bp = Bp
+            if Bp != B:
+                xp = torch.zeros((Bp, self.F), dtype=torch.float32, device=self.device)
+                xp[:B].copy_(x)
+                x = xp
+            self._xq = torch.empty(lib.b200ds_fh_operand_bytes(Bp, self.F), dtype=torch.uint8, device=self.device)
+            self._hT = torch.empty(lib.b200ds_fh_operand_bytes(self.H, Bp), dtype=torch.uint8, device=self.device)
+            if self._wq is None:
+                self._wq = torch.empty(lib.b200ds_fh_operand_bytes(self.H, self.F), dtype=torch.uint8, device=self.device)
+            _lib.check(lib.b200ds_fh_pack_bf16(x.data_ptr(), Bp, self.F, self._xq.data_ptr(), stream), "fh_pack_bf16(x)")
+            if self._wq_step != self.global_steps:
+                _lib.check(lib.b200ds_fh_pack_bf16(self.flat.data_ptr(), self.H, self.F, self._wq.data_ptr(), stream), "fh_pack_bf16(W1)")
+                self._wq_step = self.global_steps
+            need = lib.b200ds_fh_forward_scratch_bytes(Bp, self.F, self.H)
+            if self._fwd_scratch is None or self._fwd_scratch.numel() < need:
+                self._fwd_scratch = torch.zeros(max(need, 256), dtype=torch.uint8, device=self.device)
+            logits_p = torch.empty(Bp, dtype=torch.float32, device=self.device)
+            _lib.check(lib.b200ds_fh_forward(self._xq.data_ptr(), self._wq.data_ptr(), self.flat.data_ptr(), Bp, self.F, self.H,
+                                             self._hT.data_ptr(), self._fwd_scratch.data_ptr(), self._fwd_scratch.numel(), stream), "fh_forward")
+            _lib.check(lib.b200ds_fh_logits(self._fwd_scratch.data_ptr(), self.flat.data_ptr(), Bp, self.F, self.H, logits_p.data_ptr(),
+                                            stream), "fh_logits")
+            logits = logits_p[:B].view(B, 1)
+        elif self._tc:
             # bf16 extension (BASELINE config 3/4): tcgen05 kernels on packed bf16 operands; the batch is padded to
             # a multiple of 128 rows inside the pack (zero rows, whose dlogits backward() keeps at zero)
             Bp = (B + 127) // 128 * 128
@@ -216,7 +246,15 @@ class B200Engine:
             dlogits = dlogits.contiguous()
         B = self._x.shape[0]
         stream = _lib.current_stream()
-        if self._tc:
+        if self._tc and self._wide:
+            Bp = self._Bp
+            dzp = torch.zeros(Bp, dtype=torch.float32, device=self.device)      # padded rows carry dlogits = 0
+            dzp[:B].copy_(dlogits.reshape(-1))
+            scratch = self._scratch_for(self.lib.b200ds_fh_backward_scratch_bytes(Bp, self.F, self.H))
+            _lib.check(self.lib.b200ds_fh_backward(self._xq.data_ptr(), self._hT.data_ptr(), dzp.data_ptr(), self.flat.data_ptr(), Bp,
+                                                   self.F, self.H, self.grads.data_ptr(), scratch.data_ptr(), scratch.numel(), stream),
+                       "fh_backward")
+        elif self._tc:
             Bp = self._Bp
             if Bp != B:                       # padded rows carry dlogits = 0: they add nothing to any gradient
                 dzp = torch.zeros(Bp, dtype=torch.float32, device=self.device)

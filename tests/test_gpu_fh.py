@@ -227,3 +227,38 @@ def test_fh_n_steps_track_fp32_autograd(lib, cuda_dev):
         a, r, z0 = p_e[o:o + cnt].double(), ref[o:o + cnt].double(), flat0[o:o + cnt].double()
         assert float((a - r).norm()) <= 2e-2 * float(r.norm()), (name, float((a - r).norm() / r.norm()))
         assert float((a - r).norm()) <= 1e-1 * float((r - z0).norm()), (name, float((a - r).norm() / (r - z0).norm()))
+
+
+def test_engine_routes_wide_inputs_through_the_gemm_path(cuda_dev):
+    """deepspeed-style calls on a model with n_features = 512: bf16.enabled sends engine(x) / backward / step through the
+    wide-input kernels (batch of 300 padded to 2048 rows, hidden 192 to 256); six steps track the oracle's fp32 step on
+    the same batches within north_star's bf16 tolerance, the padded hidden units stay zero."""
+    import b200ds
+    F, H, B, steps = 512, 192, 300, 6
+    torch.manual_seed(21)
+    net = torch.nn.Sequential(torch.nn.Linear(F, H), torch.nn.ReLU(), torch.nn.Linear(H, 1))
+    p = {"w1": net[0].weight.detach().clone(), "b1": net[0].bias.detach().clone(),
+         "w2": net[2].weight.detach().clone(), "b2": net[2].bias.detach().clone()}
+    opt = torch.optim.Adam(net.parameters(), lr=1e-3)
+    engine, _, _, _ = b200ds.initialize(model=net, optimizer=opt, config={"bf16": {"enabled": True}, "zero_optimization": {"stage": 0}})
+    assert engine._wide and engine.H == 256
+    crit = b200ds.BCEWithLogitsLoss()
+    flat = ora.flatten(p)
+    st = ora.AdamState()
+    for s in range(steps):
+        x = torch.randn(B, F)
+        y = ora.label_rule(x)
+        logits = engine(x.to(cuda_dev))
+        assert logits.shape == (B, 1)
+        loss = crit(logits, y.to(cuda_dev))
+        engine.backward(loss)
+        engine.step()
+        pp = ora.unflatten(flat, F, H)
+        z, h = ora.forward(pp, x)
+        want = float(ora.bce_with_logits(z, y))
+        ora.adam_update(flat, ora.flatten(ora.backward(pp, x, y, z, h)), st, 1e-3)
+        assert abs(loss.item() - want) <= 2e-2 * abs(want), (s, loss.item(), want)
+    got = torch.cat([t.detach().reshape(-1).cpu() for t in (net[0].weight, net[0].bias, net[2].weight, net[2].bias)])
+    assert float((got - flat).norm()) <= 2e-2 * float(flat.norm())
+    fl = engine.flat.cpu()
+    assert float(fl[H * F: 256 * F].abs().max()) == 0.0          # padded W1 rows
