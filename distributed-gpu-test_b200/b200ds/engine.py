@@ -172,6 +172,7 @@ class B200Engine:
                              % (self.F, self.device, x.dtype, tuple(x.shape), x.device))
         x = x.contiguous()
         B = x.shape[0]
+        self._nrows = B                        # the caller's batch (the kernels may see it padded)
         stream = _lib.current_stream()
         self._tc = self.cfg["precision"] == "bf16"
         if self._tc and self._wide:
@@ -244,7 +245,7 @@ class B200Engine:
             # derivative w.r.t. our logits from autograd, everything below is ours again.
             (dlogits,) = torch.autograd.grad(loss, self._logits)
             dlogits = dlogits.contiguous()
-        B = self._x.shape[0]
+        B = self._nrows
         stream = _lib.current_stream()
         if self._tc and self._wide:
             Bp = self._Bp
