@@ -232,6 +232,12 @@ pack_w1_kernel(const float* __restrict__ params, Layout L, uint4* __restrict__ w
 // UMMA operand reads, which already use the full 128 B/clk), and each thread keeps 64 running
 // sums acc[b] += w2[n] |z1[n,b]| across all chunks of the tile.  The sum over n (lanes, then
 // the 4 lane quadrants) happens once per tile.
+#ifdef B200DS_TRACE      // tuning builds only (tools/build_variant.sh trace "-DB200DS_TRACE", tools/tc_trace.py): clock64 stamps of CTA 0
+__device__ long long g_trace[24 * 128 * 4];      // [role][chunk or group][event]
+#define B200_TRACE(role, q, ev) do { if (blockIdx.x == 0 && lane == 0 && (q) < 128) g_trace[(((role) * 128) + (q)) * 4 + (ev)] = clock64(); } while (0)
+#else
+#define B200_TRACE(role, q, ev) do { } while (0)
+#endif
 constexpr int kFwdXStages = 3;
 constexpr int kFwdRing = 4;               // D1T accumulators in TMEM: 4 x 128 columns
 constexpr int kFwdEpiWarps = 8;           // warp (quad, half): 32 lanes (n) x 64 columns (b)
@@ -241,11 +247,11 @@ constexpr int kFwdThreads = 32 * 12;      // warps 0-7 epilogue, warp 8 TMA, war
 
 struct FwdSmem {                           // fixed-size tail after the W1 slice / w2 slice / x stages
   float v[32];
-  float red[2][4][64];                     // [column half][lane quadrant][column]: per-warp column sums
+  float red[2][2][4][64];                  // [tile parity][column half][lane quadrant][column]: per-warp column sums
   uint64_t w_bar, x_full[kFwdXStages], x_free[kFwdXStages], d1_full[kFwdRing], d1_free[kFwdRing];
   uint32_t tmem_slot;
-  float zt[2][kTileRows];                  // slice sum: this CTA's part of a tile's logits, by tile parity
-  uint64_t z_full[2], z_free[2];
+  uint64_t z_full[2], z_free[2];           // red[parity] handed to the finishing warp / given back
+  uint64_t v_ready;                        // v[] (formed by the epilogue warps in the prologue) may be read by the finishing warp
 };
 
 // sum over the 32 lanes of 64 per-lane values; lane l ends with the totals of columns
@@ -284,12 +290,13 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
 
   if (threadIdx.x == 0) {
     mbar_init(&sh->w_bar, 1);
-    // an x stage has two kinds of readers: the MMAs (released by the issuers' tcgen05.commit) and the four
-    // half-0 epilogue warps, which read the tile's rows for the linear term -- both must be done with it
-    // before the producer may refill the stage (with NG <= RING the MMAs alone run a whole ring ahead)
-    for (int i = 0; i < kFwdXStages; ++i) { mbar_init(&sh->x_full[i], 1); mbar_init(&sh->x_free[i], n_issuers + 4); }
+    // an x stage has two kinds of readers: the MMAs (released by the issuers' tcgen05.commit) and the finishing
+    // warp, which reads the tile's rows for the linear term -- both must be done with it before the producer may
+    // refill the stage (with NG <= RING the MMAs alone run a whole ring ahead)
+    for (int i = 0; i < kFwdXStages; ++i) { mbar_init(&sh->x_full[i], 1); mbar_init(&sh->x_free[i], n_issuers + 1); }
     for (int i = 0; i < kFwdRing; ++i) { mbar_init(&sh->d1_full[i], 1); mbar_init(&sh->d1_free[i], kFwdEpiWarps); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&sh->z_full[i], 4); mbar_init(&sh->z_free[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&sh->z_full[i], kFwdEpiWarps); mbar_init(&sh->z_free[i], 1); }
+    mbar_init(&sh->v_ready, 1);
     mbar_fence_init();
     // start the 128 KB W1 slice right away: it overlaps the rest of the prologue
     const unsigned char* wsrc = w1q + (size_t)slice * slice_rows * KP * 2;
@@ -309,16 +316,17 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
       const float* vp = vlin + (size_t)slice * nblk * 32 + lane;
       float a = 0.f;
       for (int i = warp; i < nblk; i += 8) a += vp[(size_t)i * 32];
-      sh->red[0][0][warp * 32 + lane] = a;      // red[] is free until the first tile ends
+      (&sh->red[0][0][0][0])[warp * 32 + lane] = a;      // red[] is free until the first tile ends
     }
     asm volatile("bar.sync 1, 256;" ::: "memory");
     if (threadIdx.x < 32) {
       float a = 0.f;
 #pragma unroll
-      for (int w = 0; w < 8; ++w) a += (&sh->red[0][0][0])[w * 32 + threadIdx.x];
+      for (int w = 0; w < 8; ++w) a += (&sh->red[0][0][0][0])[w * 32 + threadIdx.x];
       sh->v[threadIdx.x] = a;
     }
     asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (threadIdx.x == 0) mbar_arrive(&sh->v_ready);
   }
   if (sh->tmem_slot != 0) __trap();        // all 512 columns are ours: the allocation can only start at 0,
   constexpr uint32_t tmem = 0;             // and a literal keeps the MMA issue path free of vector -> uniform moves
@@ -358,8 +366,10 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
           const uint32_t rph = (uint32_t)(gq / RING) & 1u;
           const uint64_t wd = wdesc0 + (uint64_t)((g * G * kTileBytes) >> 4);
           const uint32_t dcol = tmem + r * (128 * G);
+          B200_TRACE(me, gq, 0);
           mbar_wait(&sh->d1_free[r], rph ^ 1);
           tc_fence_after();
+          B200_TRACE(me, gq, 1);
           if (elect_one()) {
 #pragma unroll
             for (int j = 0; j < G; ++j) {
@@ -369,6 +379,7 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
             mma_commit(&sh->d1_full[r]);
           }
           __syncwarp();
+          B200_TRACE(me, gq, 2);
         }
         if (elect_one()) mma_commit(&sh->x_free[s]);
         __syncwarp();
@@ -378,74 +389,83 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
     if (warp == 9) issue(std::integral_constant<int, 0>{});
     else issue(std::integral_constant<int, 1>{});
   } else if (warp == 11) {
-    // ===== slice sum (H > 2048: several slices of hidden units, in different CTAs, add into one logit).  Each CTA
-    // writes its part of a tile; whoever draws the LAST of the tile's n_slices tickets adds the parts up in slice
-    // order: bit-reproducible whichever slice was faster, and nothing to zero beforehand.  A warp of its own, so that
-    // the fences and the L2 round trips of the ticket and of the parts run beside the next tile's arithmetic (inside
-    // the epilogue warps they cost 7 us of a 38 us kernel). =====
-    if (n_slices > 1) {
-      const float b2 = b2p[0];
-      const size_t nrows = (size_t)n_btiles * kTileRows;
-      int it = 0;
-      for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice, ++it) {
-        const int b = it & 1;
-        mbar_wait(&sh->z_full[b], (uint32_t)(it >> 1) & 1u);
-        float z[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) z[j] = sh->zt[b][lane + 32 * j];
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sh->z_free[b]);
-        const size_t g0 = (size_t)t * kTileRows + lane;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) __stcg(zpart + (size_t)slice * nrows + g0 + 32 * j, z[j]);
-        __threadfence();
-        __syncwarp();
-        unsigned tk = 0;
-        if (lane == 0) tk = atomicAdd(&tickets[t], 1u);
-        tk = __shfl_sync(0xffffffffu, tk, 0);
-        if (tk == (unsigned)(n_slices - 1)) {
-          __threadfence();
-          float zs[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) zs[j] = __ldcg(zpart + g0 + 32 * j);
-          for (int sl = 1; sl < n_slices; ++sl) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) zs[j] += __ldcg(zpart + (size_t)sl * nrows + g0 + 32 * j);
-          }
-#pragma unroll
-          for (int j = 0; j < 4; ++j) logits[g0 + 32 * j] = zs[j] + b2;
-          if (lane == 0) tickets[t] = 0u;
-        }
-      }
-    }
-  } else {
-    // ===== epilogue: 8 warps on every chunk =====
-    const int half = warp >> 2, quad = warp & 3;
-    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
-    const int row = quad * 32 + lane;                      // the b row this thread finishes (half 0 warps only)
+    // ===== finisher: per tile, rows lane + 32 j.  It forms the linear half of relu itself, lin = xq[row,:] . v, from the x
+    // tile; takes the eight epilogue warps' column sums (red[parity], one mbarrier hand-over: the epilogue warps do not
+    // meet at a barrier at the end of a tile, each goes on to the next tile when its own fold is done); adds the four
+    // lane quadrants in a fixed order; z = (lin + sum) / 2 [+ b2].  With several slices of hidden units (H > 2048, in
+    // different CTAs) the CTA's part goes to global memory and whoever draws the LAST of the tile's n_slices tickets
+    // adds the parts up in slice order: bit-reproducible whichever slice was faster, nothing to zero beforehand.  All
+    // of it -- fences, L2 round trips of the ticket and of the parts -- runs beside the next tile's arithmetic. =====
     const float b2 = b2p[0];
-    int it = 0;
-    int s = 0; uint32_t xph = 0; int gq = 0;
-    for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice) {
-      float lin = 0.f;
-      if (half == 0) {       // linear half of relu: xq[row,:] . v, from the x tile in smem
-        mbar_wait(&sh->x_full[s], xph);
+    const size_t nrows = (size_t)n_btiles * kTileRows;
+    int s = 0; uint32_t xph = 0; int it = 0;
+    mbar_wait(&sh->v_ready, 0);
+    for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice, ++it) {
+      float lin[4] = {0.f, 0.f, 0.f, 0.f};
+      mbar_wait(&sh->x_full[s], xph);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int row = lane + 32 * j;
         const unsigned char* xr = xs + s * kTileBytes + (size_t)(row >> 3) * SBO_K + (size_t)(row & 7) * 16;
 #pragma unroll
         for (int c = 0; c < KP / 8; ++c) {
           uint4 qv = *reinterpret_cast<const uint4*>(xr + c * LBO_K);
           const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&qv);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            float2 f = __bfloat1622float2(h2[j]);
-            lin = fmaf(f.x, sh->v[c * 8 + 2 * j], lin);
-            lin = fmaf(f.y, sh->v[c * 8 + 2 * j + 1], lin);
+          for (int e = 0; e < 4; ++e) {
+            float2 f = __bfloat1622float2(h2[e]);
+            lin[j] = fmaf(f.x, sh->v[c * 8 + 2 * e], lin[j]);
+            lin[j] = fmaf(f.y, sh->v[c * 8 + 2 * e + 1], lin[j]);
           }
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&sh->x_free[s]);        // this warp's rows of the stage are in registers
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sh->x_free[s]);            // the rows of the stage are in registers
       if (++s == kFwdXStages) { s = 0; xph ^= 1; }
+      const int b = it & 1;
+      mbar_wait(&sh->z_full[b], (uint32_t)(it >> 1) & 1u);
+      float z[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int row = lane + 32 * j, hb = row >> 6, cb = row & 63;
+        const float ab = (sh->red[b][hb][0][cb] + sh->red[b][hb][1][cb]) + (sh->red[b][hb][2][cb] + sh->red[b][hb][3][cb]);
+        z[j] = 0.5f * (lin[j] + ab);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sh->z_free[b]);
+      const size_t g0 = (size_t)t * kTileRows + lane;
+      if (n_slices == 1) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) logits[g0 + 32 * j] = z[j] + b2;
+        continue;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) __stcg(zpart + (size_t)slice * nrows + g0 + 32 * j, z[j]);
+      __threadfence();
+      __syncwarp();
+      unsigned tk = 0;
+      if (lane == 0) tk = atomicAdd(&tickets[t], 1u);
+      tk = __shfl_sync(0xffffffffu, tk, 0);
+      if (tk == (unsigned)(n_slices - 1)) {
+        __threadfence();
+        float zs[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) zs[j] = __ldcg(zpart + g0 + 32 * j);
+        for (int sl = 1; sl < n_slices; ++sl) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) zs[j] += __ldcg(zpart + (size_t)sl * nrows + g0 + 32 * j);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) logits[g0 + 32 * j] = zs[j] + b2;
+        if (lane == 0) tickets[t] = 0u;
+      }
+    }
+  } else {
+    // ===== epilogue: 8 warps on every chunk =====
+    const int half = warp >> 2, quad = warp & 3;
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    int it = 0, gq = 0;
+    for (int t = cta_in_slice; t < n_btiles; t += ctas_per_slice) {
       float acc[64];
 #pragma unroll
       for (int i = 0; i < 64; ++i) acc[i] = 0.f;
@@ -460,6 +480,7 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
       }
       for (int g = 0; g < NG; ++g, ++gq) {
         const int r = gq % RING;
+        B200_TRACE(2 + warp, gq, 0);
 #pragma unroll
         for (int j = 0; j < G; ++j) {
           const float w2n = w2s[(g * G + j) * kTileRows + quad * 32 + lane];
@@ -475,16 +496,19 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
             tc_fence_before();                                         // the group is fully read: release it
             __syncwarp();
             if (lane == 0) mbar_arrive(&sh->d1_free[r]);
+            B200_TRACE(2 + warp, gq, 1);
             if (g + 1 < NG) {                                          // piece 0 of the next group
               const int r1 = (gq + 1) % RING;
               mbar_wait(&sh->d1_full[r1], (uint32_t)((gq + 1) / RING) & 1u);
               tc_fence_after();
+              B200_TRACE(2 + warp, gq, 2);
               tmem_ld32(tmem + lane_base + r1 * (128 * G) + half * 64, va);
             }
           }
 #pragma unroll
           for (int i = 0; i < 32; ++i) acc[32 + i] = fmaf(fabsf(__uint_as_float(vb[i])), w2n, acc[32 + i]);
         }
+        B200_TRACE(2 + warp, gq, 3);
       }
       // ---- sum over n: 32 lanes by a transposing butterfly, then the 4 quadrants through smem
       lane_fold<64, 16>(acc, lane);
@@ -493,23 +517,12 @@ mlp_fwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
       lane_fold<8, 2>(acc, lane);
       lane_fold<4, 1>(acc, lane);
       const int col = ((lane & 16) ? 32 : 0) + ((lane & 8) ? 16 : 0) + ((lane & 4) ? 8 : 0) + ((lane & 2) ? 4 : 0) + ((lane & 1) ? 2 : 0);
-      asm volatile("bar.sync 1, 256;" ::: "memory");       // previous tile's red[] has been consumed
-      sh->red[half][quad][col] = acc[0];
-      sh->red[half][quad][col + 1] = acc[1];
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (half == 0) {
-        const int hb = row >> 6, cb = row & 63;
-        const float ab = (sh->red[hb][0][cb] + sh->red[hb][1][cb]) + (sh->red[hb][2][cb] + sh->red[hb][3][cb]);
-        const float z = 0.5f * (lin + ab);
-        if (n_slices == 1) {
-          logits[(size_t)t * kTileRows + row] = z + b2;
-        } else {                                           // this CTA's part of the tile -> the slice-sum warp
-          const int b = it & 1;
-          mbar_wait(&sh->z_free[b], ((uint32_t)(it >> 1) & 1u) ^ 1u);
-          sh->zt[b][row] = z;
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&sh->z_full[b]);
-        }
+      {                                                    // this warp's column sums -> the finishing warp
+        const int b = it & 1;
+        mbar_wait(&sh->z_free[b], ((uint32_t)(it >> 1) & 1u) ^ 1u);
+        *reinterpret_cast<float2*>(&sh->red[b][half][quad][col]) = make_float2(acc[0], acc[1]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sh->z_full[b]);
       }
       ++it;
     }
@@ -653,14 +666,17 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         for (int i = 0; i < nb; ++i) {
           const uint64_t wd = wdesc0 + (uint64_t)((i * kTileBytes) >> 4);
           const uint32_t dcol = tmem + r * 128;
+          B200_TRACE(10, (t - t_begin) * nb + i, 0);
           mbar_wait(&sh->d1_free[r], rph ^ 1);
           tc_fence_after();
+          B200_TRACE(10, (t - t_begin) * nb + i, 1);
           if (elect_one()) {
             mma_ss(dcol, wd, xd, idesc, 0);
             mma_ss(dcol, wd + (2 * LBO_K >> 4), xd + (2 * LBO_K >> 4), idesc, 1);
             mma_commit(&sh->d1_full[r]);
           }
           __syncwarp();
+          B200_TRACE(10, (t - t_begin) * nb + i, 2);
           if (++r == kBwdRing) { r = 0; rph ^= 1; }
         }
         if (++s == kBwdXStages) { s = 0; xph ^= 1; }
@@ -683,8 +699,10 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
           const int r = q % kBwdRing;
           const uint32_t rph = (uint32_t)(q / kBwdRing) & 1u;
           const uint32_t scol = tmem + s_col0 + i * 32, acol = tmem + r * 128;
+          B200_TRACE(11, q, 0);
           mbar_wait(&sh->a_ready[r], rph);
           tc_fence_after();
+          B200_TRACE(11, q, 1);
           if (elect_one()) {
             mma_ts(scol, acol, gd, idesc, first);
 #pragma unroll
@@ -693,6 +711,7 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
             mma_commit(&sh->d1_free[r]);
           }
           __syncwarp();
+          B200_TRACE(11, q, 2);
         }
         if (elect_one()) mma_commit(&sh->x_free[s]);
         __syncwarp();
@@ -714,8 +733,10 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         const int r = q % kBwdRing;
         const uint32_t rph = (uint32_t)(q / kBwdRing) & 1u;
         if (!dz_waited) { mbar_wait(&sh->dz_full[s], xph); dz_waited = true; }
+        B200_TRACE(12 + quad, q, 0);
         mbar_wait(&sh->d1_full[r], rph);
         tc_fence_after();
+        B200_TRACE(12 + quad, q, 1);
         const uint4* dzp = reinterpret_cast<const uint4*>(sh->dzs[s]);
         const uint32_t tbase = tmem + lane_base + r * 128;
         uint32_t va[32], vb[32], vc[32];
@@ -749,10 +770,12 @@ mlp_bwd_tc_kernel(const unsigned char* __restrict__ xq, const unsigned char* __r
         B200_BWD_CONVERT(2, vc)
         B200_BWD_CONVERT(3, va)
 #undef B200_BWD_CONVERT
+        B200_TRACE(12 + quad, q, 2);
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&sh->a_ready[r]);
+        B200_TRACE(12 + quad, q, 3);
       }
       if (++s == kBwdXStages) { s = 0; xph ^= 1; }
     }
@@ -1037,6 +1060,15 @@ static bool bwd_plan(int64_t batch, int H, BwdPlan* p) {
 using namespace b200ds;
 
 extern "C" {
+
+#ifdef B200DS_TRACE
+B200DS_API int b200ds_debug_trace(long long* out_host, size_t n, int clear) {      // tuning builds only; not part of the ABI
+  B200_CUDA(cudaDeviceSynchronize());
+  if (out_host) B200_CUDA(cudaMemcpyFromSymbol(out_host, g_trace, n * sizeof(long long)));
+  if (clear) { void* p = nullptr; B200_CUDA(cudaGetSymbolAddress(&p, g_trace)); B200_CUDA(cudaMemset(p, 0, sizeof(long long) * 24 * 128 * 4)); }
+  return B200DS_OK;
+}
+#endif
 
 int b200ds_tc_supported(int64_t batch, int n_features, int hidden) {
   FwdPlan fp;
