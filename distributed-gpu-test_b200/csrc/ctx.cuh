@@ -30,6 +30,8 @@ struct b200ds_ctx {
   cudaStream_t cap = nullptr;
   unsigned long long* step_word = nullptr;     // device
   unsigned long long* step_pinned = nullptr;   // pinned host
+  bool step_word_known = false;                // the host knows what step_word holds (it is only written by this context's graphs and copies)
+  int64_t step_word_value = 0;
   // peer-memory exchange (b200ds_ctx_enable_p2p): every rank's exchange buffer and flag row,
   // own entries cudaMalloc'ed here, the others opened from the peers' IPC handles
   float* p2p_xchg[B200DS_P2P_MAX_WORLD] = {};

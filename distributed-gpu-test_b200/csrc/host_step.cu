@@ -26,7 +26,8 @@ size_t b200ds_train_step_scratch_bytes(int64_t batch, int n_features, int hidden
 // the device part of the step on staged inputs (x_dev, y_dev), loss left in b->loss
 static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const float* x_dev, const float* y_dev,
                            int64_t batch, int n_features, int hidden, double lr, double beta1, double beta2,
-                           double eps, int64_t step0, const uint64_t* step_counter /* device word holding step0 + 1, or NULL */,
+                           double eps, int64_t step0, uint64_t* step_counter /* graph replay: device word holding step0 when the step starts;
+                           the loss kernel of the step makes it step0 + 1, the optimizer reads it.  NULL: eager, step0 + 1 by value */,
                            uintptr_t stream) {
   const Layout L{n_features, hidden};
   const int64_t P = L.count();
@@ -60,7 +61,7 @@ static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const flo
     if ((rc = b200ds_fh_pack_bf16(b->params, hidden, n_features, b->wq, stream))) return rc;
     if ((rc = b200ds_fh_forward(b->xq, b->wq, b->params, batch, n_features, hidden, hT, fwd_sc, fwd_b, stream))) return rc;
     if ((rc = b200ds_fh_logits(fwd_sc, b->params, batch, n_features, hidden, b->logits, stream))) return rc;
-    if ((rc = b200ds_bce_loss_grad(b->logits, y_dev, batch, b->loss, b->dlogits, nullptr, sc, bce_bytes, stream))) return rc;
+    if ((rc = b200ds_bce_loss_grad(b->logits, y_dev, batch, b->loss, b->dlogits, step_counter, sc, bce_bytes, stream))) return rc;
     if ((rc = b200ds_fh_backward(b->xq, hT, b->dlogits, b->params, batch, n_features, hidden, b->grads, bwd_sc, bwd_b, stream))) return rc;
     if ((rc = b200ds_allreduce_bucket(ctx, b->grads, P, stream))) return rc;
     if (step_counter)
@@ -78,10 +79,20 @@ static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const flo
     if ((rc = b200ds_mlp_forward_f32(b->params, x_dev, batch, n_features, hidden, b->logits, stream))) return rc;
   }
   if (use_tc) {       // criterion + backward in one pass (dlogits is not materialised on this path)
+    char* bwd_sc = sc + bce_bytes;
+    const size_t bwd_bytes = need - bce_bytes - align_up(b200ds_mlp_forward_tc_scratch_bytes(batch, n_features, hidden), 256);
+    if (ctx->world == 1 || ctx->p2p_cap >= b200ds_update_tc_exchange_elems(hidden)) {
+      // the split partials stay in scratch; finish pass + gradient exchange (several ranks: peer memory) + Adam + the next
+      // step's operand pack are one kernel (two with several ranks) instead of finish, all-reduce, Adam
+      if ((rc = b200ds_mlp_loss_backward_partials_tc(b->xq, b->wq, b->logits, y_dev, batch, n_features, hidden, step_counter,
+                                                     bwd_sc, bwd_bytes, stream))) return rc;
+      return b200ds_update_tc(ctx, bwd_sc, bwd_bytes, batch, n_features, hidden, b->params, b->grads, b->exp_avg, b->exp_avg_sq, b->wq,
+                              lr, beta1, beta2, eps, step0 + 1, step_counter, b->loss, stream);
+    }
     if ((rc = b200ds_mlp_loss_backward_tc(b->xq, b->wq, b->params, b->logits, y_dev, batch, n_features, hidden, b->loss,
-                                          b->grads, nullptr, sc + bce_bytes, need - bce_bytes - align_up(b200ds_mlp_forward_tc_scratch_bytes(batch, n_features, hidden), 256), stream))) return rc;
+                                          b->grads, step_counter, bwd_sc, bwd_bytes, stream))) return rc;
   } else {
-    if ((rc = b200ds_bce_loss_grad(b->logits, y_dev, batch, b->loss, b->dlogits, nullptr, sc, bce_bytes, stream))) return rc;
+    if ((rc = b200ds_bce_loss_grad(b->logits, y_dev, batch, b->loss, b->dlogits, step_counter, sc, bce_bytes, stream))) return rc;
     if ((rc = b200ds_mlp_backward_f32(b->params, x_dev, b->dlogits, batch, n_features, hidden, b->grads,
                                       sc + bce_bytes, need - bce_bytes - align_up(b200ds_mlp_forward_tc_scratch_bytes(batch, n_features, hidden), 256), stream))) return rc;
   }
@@ -98,8 +109,9 @@ static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const flo
 
 // The same device work as a CUDA graph: captured once per (buffers, staging half, shape, hyper-parameters) on
 // the context's capture stream, replayed on the caller's stream.  The eager call costs ~8 kernel launches of
-// host time per step; the replay one.  The Adam step number is the only thing that changes between replays:
-// it is copied into a device word before each launch.
+// host time per step; the replay one.  The Adam step number is the only thing that changes between replays: it lives
+// in a device word that the step's loss kernel increments; the host writes it only when a call's step0 is not the
+// previous call's step0 + 1 (first call, restart from a checkpoint) -- no copy in front of the graph otherwise.
 static int run_staged_step_graph(b200ds_ctx* ctx, const b200ds_step_bufs* b, int slot, const float* x_dev, const float* y_dev,
                                  int64_t batch, int n_features, int hidden, double lr, double beta1, double beta2,
                                  double eps, int64_t step0, cudaStream_t s) {
@@ -121,7 +133,7 @@ static int run_staged_step_graph(b200ds_ctx* ctx, const b200ds_step_bufs* b, int
     if (g.exec) { B200_CUDA(cudaGraphExecDestroy(g.exec)); g.exec = nullptr; }
     cudaGraph_t graph = nullptr;
     B200_CUDA(cudaStreamBeginCapture(ctx->cap, cudaStreamCaptureModeThreadLocal));
-    int rc = run_staged_step(ctx, b, x_dev, y_dev, batch, n_features, hidden, lr, beta1, beta2, eps, step0, reinterpret_cast<const uint64_t*>(ctx->step_word),
+    int rc = run_staged_step(ctx, b, x_dev, y_dev, batch, n_features, hidden, lr, beta1, beta2, eps, step0, reinterpret_cast<uint64_t*>(ctx->step_word),
                              (uintptr_t)ctx->cap);
     cudaError_t e = cudaStreamEndCapture(ctx->cap, &graph);
     if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
@@ -132,9 +144,17 @@ static int run_staged_step_graph(b200ds_ctx* ctx, const b200ds_step_bufs* b, int
     memcpy(g.key, key, n);
     g.key_len = n;
   }
-  *ctx->step_pinned = (unsigned long long)(step0 + 1);
-  B200_CUDA(cudaMemcpyAsync(ctx->step_word, ctx->step_pinned, sizeof(unsigned long long), cudaMemcpyHostToDevice, s));
-  B200_CUDA(cudaGraphLaunch(g.exec, s));
+  if (!ctx->step_word_known || ctx->step_word_value != step0) {
+    // step_pinned may still be the source of an earlier copy that has not run: one word per write would be needed to
+    // make this asynchronous; out-of-sequence steps are rare, so wait for the stream instead
+    B200_CUDA(cudaStreamSynchronize(s));
+    *ctx->step_pinned = (unsigned long long)step0;
+    B200_CUDA(cudaMemcpyAsync(ctx->step_word, ctx->step_pinned, sizeof(unsigned long long), cudaMemcpyHostToDevice, s));
+  }
+  cudaError_t le = cudaGraphLaunch(g.exec, s);
+  ctx->step_word_known = le == cudaSuccess;
+  ctx->step_word_value = step0 + 1;        // what the word holds once this replay's loss kernel has run
+  B200_CUDA(le);
   return B200DS_OK;
 }
 
@@ -187,6 +207,14 @@ int b200ds_train_step_host_prefetch(b200ds_ctx* ctx, const b200ds_step_bufs* b,
   float* xs = b->x_stage + (size_t)slot * batch * n_features;
   float* ys = b->y_stage + (size_t)slot * batch;
   ctx->pf_x = ctx->pf_y = nullptr;
+  // the staged kernels as one graph replay (the one-launch tiny class stays eager)
+  int rc = tiny_class(batch, n_features, hidden)
+               ? run_staged_step(ctx, b, xs, ys, batch, n_features, hidden, lr, beta1, beta2, eps, step0, nullptr, stream)
+               : run_staged_step_graph(ctx, b, slot, xs, ys, batch, n_features, hidden, lr, beta1, beta2, eps, step0, s);
+  if (rc) return rc;
+  B200_CUDA(cudaMemcpyAsync(loss_host, b->loss, sizeof(float), cudaMemcpyDeviceToHost, s));
+  // The next batch's copy is queued AFTER this step's kernels: the caller waits for the loss below, so every host call
+  // in front of the graph launch is GPU idle time; behind it, it costs nothing.
   if (x_next_host) {                         // the other half is idle: the previous call's work on it has been synchronised
     float* xn = b->x_stage + (size_t)(slot ^ 1) * batch * n_features;
     float* yn = b->y_stage + (size_t)(slot ^ 1) * batch;
@@ -196,12 +224,6 @@ int b200ds_train_step_host_prefetch(b200ds_ctx* ctx, const b200ds_step_bufs* b,
     ctx->pf_x = x_next_host; ctx->pf_y = y_next_host; ctx->pf_slot = slot ^ 1;
     ctx->pf_batch = batch; ctx->pf_F = n_features;      // the staged copy has THIS call's shape; a call with another shape re-copies
   }
-  // the staged kernels as one graph replay (the one-launch tiny class stays eager)
-  int rc = tiny_class(batch, n_features, hidden)
-               ? run_staged_step(ctx, b, xs, ys, batch, n_features, hidden, lr, beta1, beta2, eps, step0, nullptr, stream)
-               : run_staged_step_graph(ctx, b, slot, xs, ys, batch, n_features, hidden, lr, beta1, beta2, eps, step0, s);
-  if (rc) return rc;
-  B200_CUDA(cudaMemcpyAsync(loss_host, b->loss, sizeof(float), cudaMemcpyDeviceToHost, s));
   B200_CUDA(cudaStreamSynchronize(s));
   return B200DS_OK;
 }
