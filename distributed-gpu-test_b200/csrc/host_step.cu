@@ -81,9 +81,11 @@ static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const flo
   if (use_tc) {       // criterion + backward in one pass (dlogits is not materialised on this path)
     char* bwd_sc = sc + bce_bytes;
     const size_t bwd_bytes = need - bce_bytes - align_up(b200ds_mlp_forward_tc_scratch_bytes(batch, n_features, hidden), 256);
-    if (ctx->world == 1 || ctx->p2p_cap >= b200ds_update_tc_exchange_elems(hidden)) {
-      // the split partials stay in scratch; finish pass + gradient exchange (several ranks: peer memory) + Adam + the next
-      // step's operand pack are one kernel (two with several ranks) instead of finish, all-reduce, Adam
+    if (ctx->world == 1) {
+      // the split partials stay in scratch; finish pass + Adam + the operand pack are one kernel instead of three.  (With
+      // several ranks the same kernel family does the exchange over peer memory in three launches; in this single-stream
+      // step, with nothing to run beside them, that measured slower than finish + the one-launch all-reduce + Adam kernel
+      // below: 144.7 against 135.5 us per call at 2 GPUs.)
       if ((rc = b200ds_mlp_loss_backward_partials_tc(b->xq, b->wq, b->logits, y_dev, batch, n_features, hidden, step_counter,
                                                      bwd_sc, bwd_bytes, stream))) return rc;
       return b200ds_update_tc(ctx, bwd_sc, bwd_bytes, batch, n_features, hidden, b->params, b->grads, b->exp_avg, b->exp_avg_sq, b->wq,

@@ -389,10 +389,10 @@ B200DS_API int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* b
                            const float* x_host, const float* y_host, int64_t batch,
                            int n_features, int hidden, double lr, double beta1, double beta2,
                            double eps, int64_t step0, float* loss_host, uintptr_t stream);
-/* The same step with the NEXT batch's host->device copy started on the context's own copy
- * stream before this batch is computed -- what DataLoader workers + pin_memory give the
- * reference loop (train.py:36-44,104): the copy of batch k+1 hides behind the kernels of batch
- * k.  x_stage / y_stage must hold TWO batches (2*batch*F and 2*batch floats).  The call whose
+/* The same step with the NEXT batch's host->device copy queued on the context's own copy
+ * stream right behind the launch of this batch's kernels -- what DataLoader workers + pin_memory
+ * give the reference loop (train.py:36-44,104): the copy of batch k+1 hides behind the kernels of
+ * batch k.  x_stage / y_stage must hold TWO batches (2*batch*F and 2*batch floats).  The call whose
  * (x_host, y_host) are the pointers given as (x_next_host, y_next_host) by the previous call
  * uses the staged copy and copies nothing; any other pointers are copied as in
  * b200ds_train_step_host.  A prefetched host buffer must stay unchanged until the call that
@@ -403,7 +403,12 @@ B200DS_API int b200ds_train_step_host(b200ds_ctx* ctx, const b200ds_step_bufs* b
  * b200ds_train_step_host on the same batch.  The device part of the step is captured once per
  * (buffers, staging half, shape, hyper-parameters) as a CUDA graph on a stream of the context and
  * replayed on the caller's stream (one launch per step instead of ~8); the graphs are destroyed
- * by b200ds_ctx_destroy. */
+ * by b200ds_ctx_destroy.  The Adam step number lives in a device word of the context that the step's
+ * loss kernel increments; the host rewrites it (after a stream synchronise) only when step0 is not the
+ * previous call's step0 + 1.  With bf16 packs, a supported shape and one rank the gradients take the
+ * b200ds_update_tc route (finish + Adam + pack in one kernel); with several ranks finish, then
+ * b200ds_allreduce_adam_p2p when b200ds_ctx_enable_p2p succeeded, else ncclAllReduce and the Adam
+ * kernel.  bufs->wq is rewritten by the call either way, the caller never packs. */
 B200DS_API int b200ds_train_step_host_prefetch(b200ds_ctx* ctx, const b200ds_step_bufs* bufs,
                            const float* x_host, const float* y_host,
                            const float* x_next_host, const float* y_next_host, int64_t batch,
