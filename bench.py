@@ -738,7 +738,7 @@ def bench_e2e(lib, ctx, dev, wl, world, a, barrier, precision):
     grads, m, v, xs, ys, lg, dl, ls = z(Ppad), z(Ppad), z(Ppad), z(2 * B * F), z(2 * B), z(B), z(B), z(1)   # staging: two batches
     sc = torch.zeros(max(256, lib.b200ds_train_step_scratch_bytes(B, F, H)), dtype=torch.uint8, device=dev)
     tc = precision == "bf16"
-    fh = tc and bool(lib.b200ds_fh_supported(B, F, H))
+    fh = tc and bool(lib.b200ds_fh_train_supported(B, F, H))
     xq = torch.empty(lib.b200ds_fh_operand_bytes(B, F) if fh else lib.b200ds_tc_xq_bytes(B), dtype=torch.uint8, device=dev) if tc else None
     wq = torch.empty(lib.b200ds_fh_operand_bytes(H, F) if fh else lib.b200ds_tc_wq_bytes(H), dtype=torch.uint8, device=dev) if tc else None
     bufs = _lib.StepBufs(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), xs.data_ptr(), ys.data_ptr(),
@@ -782,13 +782,16 @@ def bench_e2e(lib, ctx, dev, wl, world, a, barrier, precision):
             ys[:B].copy_(yh[i % nbuf].view(-1), non_blocking=True)
     copies(3)                                # the first copies of a loop pay torch's one-time set-up for pinned sources
     torch.cuda.synchronize()
-    barrier()
-    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    c0.record()
-    copies(K)
-    c1.record()
-    barrier()
-    tc_ = torch.tensor([c0.elapsed_time(c1) / 1e3], dtype=torch.float64, device=dev)
+    best = float("inf")
+    for _ in range(3):                       # best of three passes: a single pass of 20 copies right after an idle period reads low
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        copies(K)
+        c1.record()
+        barrier()
+        best = min(best, c0.elapsed_time(c1) / 1e3)
+    tc_ = torch.tensor([best], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tc_, op=dist.ReduceOp.MAX)
     h2d = 4 * (B * F + B)

@@ -92,6 +92,7 @@ PROTOTYPES = {
     "b200ds_update_tc_end": (C.c_int, [c_ptr, c_ptr, C.c_size_t, c_i64, C.c_int, C.c_int, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                                        C.c_double, C.c_double, C.c_double, C.c_double, c_i64, c_ptr, c_ptr, c_stream]),
     "b200ds_fh_supported": (C.c_int, [c_i64, C.c_int, C.c_int]),
+    "b200ds_fh_train_supported": (C.c_int, [c_i64, C.c_int, C.c_int]),
     "b200ds_fh_operand_bytes": (C.c_size_t, [c_i64, c_i64]),
     "b200ds_fh_pack_bf16": (C.c_int, [c_ptr, c_i64, c_i64, c_ptr, c_stream]),
     "b200ds_fh_forward_scratch_bytes": (C.c_size_t, [c_i64, C.c_int, C.c_int]),

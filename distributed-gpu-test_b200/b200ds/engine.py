@@ -74,7 +74,7 @@ class B200Engine:
         self._wide = False                    # wide inputs: layer 1 as K-loop GEMMs (b200ds_fh_*)
         if self.cfg["precision"] == "bf16":
             self.H = (self.H_model + 127) // 128 * 128
-            if self.lib.b200ds_fh_supported(2048, self.F, self.H):
+            if self.lib.b200ds_fh_train_supported(2048, self.F, self.H):
                 self._wide = True
             elif not self.lib.b200ds_tc_supported(128, self.F, self.H):
                 raise NotImplementedError(

@@ -15,7 +15,7 @@ extern "C" {
 size_t b200ds_train_step_scratch_bytes(int64_t batch, int n_features, int hidden) {
   size_t f32 = b200ds_mlp_backward_f32_scratch_bytes(batch, n_features, hidden);
   size_t tcb = b200ds_mlp_backward_tc_scratch_bytes(batch, n_features, hidden);
-  if (b200ds_fh_supported(batch, n_features, hidden))      // wide inputs: [ loss | forward parts | backward parts | hT ]
+  if (b200ds_fh_train_supported(batch, n_features, hidden))      // wide inputs: [ loss | forward parts | backward parts | hT ]
     return align_up(b200ds_bce_scratch_bytes(batch), 256) + align_up(b200ds_fh_forward_scratch_bytes(batch, n_features, hidden), 256) +
            align_up(b200ds_fh_backward_scratch_bytes(batch, n_features, hidden), 256) + align_up(b200ds_fh_operand_bytes(hidden, batch), 256);
   // [ loss scratch | backward scratch (fp32 or tensor-core) | forward slice parts + tile tickets (tensor-core, H > 2048) ]
@@ -52,7 +52,7 @@ static int run_staged_step(b200ds_ctx* ctx, const b200ds_step_bufs* b, const flo
   B200_REQUIRE(b->scratch && b->scratch_bytes >= need, "train_step_host: scratch too small (%zu < %zu)", b->scratch_bytes, need);
   char* sc = reinterpret_cast<char*>(b->scratch);
   size_t bce_bytes = align_up(b200ds_bce_scratch_bytes(batch), 256);
-  if (b->xq && b->wq && b200ds_fh_supported(batch, n_features, hidden)) {
+  if (b->xq && b->wq && b200ds_fh_train_supported(batch, n_features, hidden)) {
     // wide inputs (F = H): pack, layer-1 GEMM, logits, loss, backward (relu, dW2/db1/db2, weight-gradient GEMM)
     const size_t fwd_b = align_up(b200ds_fh_forward_scratch_bytes(batch, n_features, hidden), 256);
     const size_t bwd_b = align_up(b200ds_fh_backward_scratch_bytes(batch, n_features, hidden), 256);

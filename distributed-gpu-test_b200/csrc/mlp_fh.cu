@@ -506,6 +506,12 @@ extern "C" {
 
 int b200ds_fh_supported(int64_t batch, int n_features, int hidden) { return fh_shape_ok(batch, n_features, hidden) ? 1 : 0; }
 
+// forward AND backward: the backward also cuts the batch into kFhRbSplits x 256 rows per CTA (relu pass) and two halves (weight gradient)
+static bool fh_train_ok(int64_t batch, int n_features, int hidden) {
+  return fh_shape_ok(batch, n_features, hidden) && (batch / 8) % (kFhRbSplits * 32) == 0 && (batch / kFhBK) % kFhWgSplits == 0;
+}
+int b200ds_fh_train_supported(int64_t batch, int n_features, int hidden) { return fh_train_ok(batch, n_features, hidden) ? 1 : 0; }
+
 size_t b200ds_fh_operand_bytes(int64_t rows, int64_t cols) { return rows > 0 && cols > 0 ? (size_t)rows * (size_t)cols * 2 : 0; }
 
 int b200ds_fh_pack_bf16(const float* src_dev, int64_t rows, int64_t cols, void* dst_dev, uintptr_t stream) {
@@ -625,7 +631,7 @@ int b200ds_fh_backward(const void* xq_dev, void* hT_dev, const float* dlogits_de
                        int n_features, int hidden, float* grads_dev, void* scratch_dev, size_t scratch_bytes, uintptr_t stream) {
   B200_REQUIRE(fh_shape_ok(batch, n_features, hidden), "fh_backward: needs F %% 256 == 0, H %% 128 == 0, batch %% 256 == 0 (got B=%lld F=%d H=%d)",
                (long long)batch, n_features, hidden);
-  B200_REQUIRE((batch / 8) % (kFhRbSplits * 32) == 0 && (batch / kFhBK) % kFhWgSplits == 0, "fh_backward: batch must be a multiple of %d", 8 * kFhRbSplits * 32);
+  B200_REQUIRE(fh_train_ok(batch, n_features, hidden), "fh_backward: batch must be a multiple of %d (b200ds_fh_train_supported)", 8 * kFhRbSplits * 32);
   B200_REQUIRE(xq_dev && hT_dev && dlogits_dev && params_dev && grads_dev, "fh_backward: null pointer");
   B200_REQUIRE((((uintptr_t)dlogits_dev) & 15) == 0 && (((uintptr_t)grads_dev) & 15) == 0, "fh_backward: dlogits / grads must be 16-byte aligned");
   const size_t need = b200ds_fh_backward_scratch_bytes(batch, n_features, hidden);

@@ -328,6 +328,9 @@ B200DS_API int b200ds_update_tc_end(b200ds_ctx* ctx, const void* scratch_dev, si
  * bytes each;  x: [batch, F], W1: [H, F], hT: [H, batch] (written by the forward, consumed by the backward).
  * b200ds_fh_pack_bf16 converts a row-major fp32 matrix (rows % 8 == 0, cols % 64 == 0). */
 B200DS_API int b200ds_fh_supported(int64_t batch, int n_features, int hidden);
+/* the same class narrowed to what the BACKWARD takes as well (batch % 2048 == 0): b200ds_train_step_host(_prefetch)
+ * routes a step to these kernels only then; any other wide shape takes the fp32 kernels. */
+B200DS_API int b200ds_fh_train_supported(int64_t batch, int n_features, int hidden);
 B200DS_API size_t b200ds_fh_operand_bytes(int64_t rows, int64_t cols);
 B200DS_API int b200ds_fh_pack_bf16(const float* src_dev, int64_t rows, int64_t cols, void* dst_dev, uintptr_t stream);
 /* model_engine(batch_x) (train.py:107) up to the per-tile parts of the logits: hT[n, b] = bf16(relu(x_q[b,:] . W1_q[n,:] + b1[n]))

@@ -1,6 +1,8 @@
 """Parity of the wide-input path (F in the hundreds / thousands: K-loop tcgen05 GEMMs fed by tensor-map TMA,
 csrc/mlp_fh.cu) through the C ABI, against an fp64 evaluation of the same bf16-operand formulas on the GPU.
 SimpleNet(n_features, hidden) takes any n_features (train.py:26-36); train.py:107,113 are the calls replaced."""
+import ctypes as C
+
 import pytest
 import torch
 
@@ -262,3 +264,34 @@ def test_engine_routes_wide_inputs_through_the_gemm_path(cuda_dev):
     assert float((got - flat).norm()) <= 2e-2 * float(flat.norm())
     fl = engine.flat.cpu()
     assert float(fl[H * F: 256 * F].abs().max()) == 0.0          # padded W1 rows
+
+
+def test_host_step_takes_wide_shapes_the_backward_cannot_cut(lib, cuda_dev):
+    """b200ds_fh_supported is the forward's shape class; the backward needs batch % 2048 == 0 on top
+    (b200ds_fh_train_supported).  A host-buffer step on a wide shape outside that (B = 256) must run -- on the fp32
+    kernels -- and not fail in the middle of the GEMM route; its loss is the oracle's fp32 loss."""
+    from b200ds import _lib
+    B, F, H = 256, 256, 128
+    assert lib.b200ds_fh_supported(B, F, H) == 1 and lib.b200ds_fh_train_supported(B, F, H) == 0
+    assert lib.b200ds_fh_train_supported(2048, F, H) == 1
+    torch.manual_seed(21)
+    p = ora.init_params(F, H)
+    flat = ora.flatten(p)
+    P = flat.numel(); Ppad = (P + 3) // 4 * 4
+    z = lambda n: torch.zeros(n, dtype=torch.float32, device=cuda_dev)      # noqa: E731
+    params = z(Ppad); params[:P] = flat.to(cuda_dev)
+    grads, m, v, xs, ys, lg, dl, ls = z(Ppad), z(Ppad), z(Ppad), z(B * F), z(B), z(B), z(B), z(1)
+    sc = torch.zeros(max(256, lib.b200ds_train_step_scratch_bytes(B, F, H)), dtype=torch.uint8, device=cuda_dev)
+    xq = torch.empty(lib.b200ds_fh_operand_bytes(B, F), dtype=torch.uint8, device=cuda_dev)
+    wq = torch.empty(lib.b200ds_fh_operand_bytes(H, F), dtype=torch.uint8, device=cuda_dev)
+    bufs = _lib.StepBufs(params.data_ptr(), grads.data_ptr(), m.data_ptr(), v.data_ptr(), xs.data_ptr(), ys.data_ptr(),
+                         lg.data_ptr(), dl.data_ptr(), ls.data_ptr(), sc.data_ptr(), sc.numel(), xq.data_ptr(), wq.data_ptr())
+    ctx = C.c_void_p()
+    _chk(lib.b200ds_ctx_create(0, 0, 1, None, C.byref(ctx)))
+    xh = torch.randn(B, F).pin_memory(); yh = ora.label_rule(xh).reshape(-1).contiguous().pin_memory(); lh = torch.zeros(1).pin_memory()
+    zref, _ = ora.forward(ora.unflatten(flat, F, H), xh.clone())
+    lref = ora.bce_with_logits(zref, yh.reshape(-1, 1).clone())
+    _chk(lib.b200ds_train_step_host(ctx, C.byref(bufs), xh.data_ptr(), yh.data_ptr(), B, F, H, 1e-3, 0.9, 0.999, 1e-8, 0,
+                                    lh.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    assert abs(float(lh) - float(lref)) <= 1e-5 * max(1.0, abs(float(lref)))      # the fp32 kernels' tolerance, not bf16's
+    _chk(lib.b200ds_ctx_destroy(ctx))

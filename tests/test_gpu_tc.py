@@ -387,13 +387,15 @@ def test_prefetching_host_step_equals_the_plain_one(lib, cuda_dev, B, F, H):
     lh = torch.zeros(1).pin_memory()
     order = [0, 1, 2, 4, 5, 3]               # step 3 consumes batch 4 although batch 3 was announced
     announce = [1, 2, 3, 5, None, None]      # step 4 announces nothing, step 5 arrives unannounced
+    step0s = [0, 1, 2, 3, 40, 41]            # the Adam step number jumps (a restart from a checkpoint): the graph path keeps it in a
+                                             # device word that its loss kernel increments and must notice a call that is out of sequence
     res = []
     for prefetch in (False, True):
         t, bufs, P = _host_step_state(lib, cuda_dev, B, F, H, 2 if prefetch else 1)
         ctx = C.c_void_p()
         _chk(lib.b200ds_ctx_create(0, 0, 1, None, C.byref(ctx)))
         losses = []
-        for step, (i, nxt) in enumerate(zip(order, announce)):
+        for step, i, nxt in zip(step0s, order, announce):
             if prefetch:
                 xn = xh[nxt].data_ptr() if nxt is not None else None
                 yn = yh[nxt].data_ptr() if nxt is not None else None
