@@ -33,6 +33,6 @@ for rep in sys.argv[1:]:
         for sub, wl, label, src in RULES:
             if sub in name:
                 out[wl] = {"kernel": label, "traffic_bytes": int(b), "dtype": "bf16", "source": src, "source_sha16": sha(src),
-                           "report": os.path.basename(rep)}
+                           "report": "profiles/" + os.path.basename(rep).replace(".ncu-rep", "").replace("r02_", "r02_ncu_") + ".txt"}
 json.dump(out, open(os.path.join(ROOT, "profiles", "ncu_traffic.json"), "w"), indent=1)
 print(json.dumps(out, indent=1))
