@@ -34,6 +34,7 @@ WORKLOADS = {
     # wide inputs ("F = H", SURVEY 8d-4: the extension where layer 1 is a real GEMM); a smaller one for quick runs
     "wideFH4096": dict(B=65536, F=4096, H=4096),
     "wideFH1024": dict(B=65536, F=1024, H=1024),
+    "wideFH8192": dict(B=65536, F=8192, H=8192),      # 67 M parameters, 17.6 TFLOP per step, 268 MB gradient bucket
 }
 SEED = 42
 LR = 1e-3

@@ -54,7 +54,7 @@ def test_fh_pack_layout(lib, cuda_dev):
     assert lib.b200ds_fh_pack_bf16(src.data_ptr(), 63, K, dst.data_ptr(), _st()) == 1
 
 
-@pytest.mark.parametrize("B,F,H", [(256, 256, 128), (512, 256, 256), (1024, 1024, 1024), (8192, 512, 384), (4096, 4096, 4096)])
+@pytest.mark.parametrize("B,F,H", [(256, 256, 128), (512, 256, 256), (1024, 1024, 1024), (8192, 512, 384), (4096, 4096, 4096), (2048, 8192, 8192)])
 def test_fh_forward_vs_fp64(lib, cuda_dev, B, F, H):
     assert lib.b200ds_fh_supported(B, F, H) == 1
     p, x, params, P, xq, wq = _setup(lib, cuda_dev, B, F, H, B + F + H)
@@ -81,7 +81,7 @@ def test_fh_forward_vs_fp64(lib, cuda_dev, B, F, H):
         assert not bool(bad.any()), (rep, int(bad.sum()), float((zp - want).abs().max()))
 
 
-@pytest.mark.parametrize("B,F,H", [(2048, 256, 128), (4096, 512, 384), (2048, 1024, 1024), (8192, 4096, 2048)])
+@pytest.mark.parametrize("B,F,H", [(2048, 256, 128), (4096, 512, 384), (2048, 1024, 1024), (8192, 4096, 2048), (2048, 8192, 8192)])
 def test_fh_backward_vs_fp64(lib, cuda_dev, B, F, H):
     p, x, params, P, xq, wq = _setup(lib, cuda_dev, B, F, H, 3 * B + F + H)
     hT = torch.empty(lib.b200ds_fh_operand_bytes(H, B), dtype=torch.uint8, device=cuda_dev)
@@ -124,7 +124,7 @@ def test_fh_backward_vs_fp64(lib, cuda_dev, B, F, H):
         assert not bool(bad.any()), (rep, int(bad.sum()), int(bad.nonzero()[0]), float((g - ref).abs().max()))
 
 
-@pytest.mark.parametrize("B,F", [(2048, 256), (4096, 1024), (8192, 4096), (512, 512), (65536, 4096)])
+@pytest.mark.parametrize("B,F", [(2048, 256), (4096, 1024), (8192, 4096), (512, 512), (65536, 4096), (4096, 8192)])
 def test_fh_generator_is_torch_randn_bit_for_bit(lib, cuda_dev, B, F):
     """b200ds_fh_gen_batch == bf16 pack of torch.randn(B*F, device='cuda') under the same seed / offset, three consecutive
     draws (the third through the device draw counter); labels = sign of the fp64 row sums of the fp32 values wherever that
