@@ -356,8 +356,18 @@ class B200Engine:
             "loss": torch.zeros(1, dtype=torch.float32, device=dev),
             "scratch": torch.zeros(max(nbytes, 256), dtype=torch.uint8, device=dev),
         }
-        use_tc = self.cfg["precision"] == "bf16" and self.lib.b200ds_tc_supported(batch, self.F, self.H)
-        if use_tc:
+        # bf16: the step takes the tensor-core kernels only when it is handed operand buffers for them, and only for
+        # batches those kernels can cut; anything else would be a silent fp32 step, which this engine does not do
+        bf16 = self.cfg["precision"] == "bf16"
+        wide = bf16 and self._wide and bool(self.lib.b200ds_fh_train_supported(batch, self.F, self.H))
+        use_tc = wide or (bf16 and not self._wide and bool(self.lib.b200ds_tc_supported(batch, self.F, self.H)))
+        if bf16 and not use_tc:
+            raise NotImplementedError("bf16.enabled: the host-buffer step needs a batch that is a multiple of %d for this model (got %d)"
+                                      % (2048 if self._wide else 128, batch))
+        if wide:
+            keep["xq"] = torch.empty(self.lib.b200ds_fh_operand_bytes(batch, self.F), dtype=torch.uint8, device=dev)
+            keep["wq"] = torch.empty(self.lib.b200ds_fh_operand_bytes(self.H, self.F), dtype=torch.uint8, device=dev)
+        elif use_tc:
             keep["xq"] = torch.empty(self.lib.b200ds_tc_xq_bytes(batch), dtype=torch.uint8, device=dev)
             keep["wq"] = torch.empty(self.lib.b200ds_tc_wq_bytes(self.H), dtype=torch.uint8, device=dev)
         bufs = _lib.StepBufs(self.flat.data_ptr(), self.grads.data_ptr(), self.exp_avg.data_ptr(),

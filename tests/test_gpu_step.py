@@ -634,3 +634,31 @@ def test_sweep_tool_and_collective_entry_point(lib, cuda_dev):
     assert lib.b200ds_collective(ctx, 3, 0, buf.data_ptr(), 64, _st()) == 1          # no such op
     assert lib.b200ds_collective(ctx, 0, 2, buf.data_ptr(), 64, _st()) == 1          # no such dtype
     _check(lib, lib.b200ds_ctx_destroy(ctx))
+
+
+def test_engine_host_buffer_step_equals_the_engine_calls(cuda_dev):
+    """engine.make_host_step (b200ds_train_step_host under the engine's own buffers: one call per step over pinned host
+    tensors) against engine(x) / backward / step on the same batches: same losses and parameters (the reference model,
+    fp32: both run the fused one-CTA kernel); and a bf16 engine refuses a batch its tensor-core kernels cannot cut
+    instead of stepping in fp32."""
+    import b200ds
+    x, y = ora.make_dataset(2000, 20, 42)
+    ea, _, _, _ = _engine_on_reference_model()
+    eb, _, _, _ = _engine_on_reference_model()
+    crit = b200ds.BCEWithLogitsLoss()
+    host_step = eb.make_host_step(4)
+    xh = torch.empty(4, 20).pin_memory(); yh = torch.empty(4).pin_memory(); lh = torch.zeros(1).pin_memory()
+    for s in range(6):
+        bi = torch.arange(s * 4, s * 4 + 4)
+        loss = crit(ea(x[bi].to(cuda_dev)), y[bi].to(cuda_dev))
+        ea.backward(loss)
+        ea.step()
+        xh.copy_(x[bi]); yh.copy_(y[bi].reshape(-1))
+        host_step(xh, yh, lh)
+        assert abs(float(lh) - loss.item()) <= 1e-6 * max(1.0, abs(loss.item())), s
+    assert eb.global_steps == ea.global_steps == 6
+    assert _rel(eb.flat[: eb.P].cpu(), ea.flat[: ea.P].cpu()) <= 1e-6
+    ec, _, _, _ = _engine_on_reference_model({"bf16": {"enabled": True}})
+    with pytest.raises(NotImplementedError):
+        ec.make_host_step(4)
+    assert callable(ec.make_host_step(128))
