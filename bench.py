@@ -2,7 +2,7 @@
 """bench.py -- train samples/s of the train.py step hot path on N B200s (one process per
 GPU), beside the reference's CPU path on the same box.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload wide4096|wide8192|tiny]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload wide4096|wide8192|wideFH4096|wideFH8192|wideFH1024|tiny]
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
     python bench.py --impl reference ...      # the reference's CPU implementation, same metric/config
 
@@ -12,6 +12,13 @@ Default workload = BASELINE.json configs[3] (widened model: F=20, H=4096, 65536
 samples/GPU), the largest single-GPU configuration and the one the metric's roofline
 fraction is defined on (the B=4 reference shape is launch-latency-bound, its
 numbers ride along under "tiny").  Prints ONE JSON line on rank 0.
+
+Environment switches, for tuning and A/B runs only (the driver's runs set none of them):
+B200DS_BENCH_NCCL=1 (W > 1: ncclAllReduce + Adam kernel instead of the peer-memory update), B200DS_BENCH_SPLIT_UPDATE=1
+(finish / exchange + Adam / pack as separate kernels), B200DS_BENCH_SEPARATE_LOSS=1 (loss kernel, then backward),
+B200DS_BENCH_SETTLE=n (clock warm-up replays; profiling runs shorten it), B200DS_BENCH_NOFLUSH=1 (no L2 flush between
+timed steps: invalid as a bench number), B200DS_BENCH_SKIP_E2E=1, B200DS_BENCH_STEP_TIMES=1 (per-step device times in the
+line), B200DS_BENCH_TRACE=1 (progress on stderr).
 """
 import argparse
 import ctypes as C
