@@ -96,3 +96,30 @@ def test_bench_reference_arm_lines(tmp_path):
     r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "2", "--warmup", "1",
                         "--workload", "tiny"], capture_output=True, text=True, env=env2, timeout=120)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_bench_traffic_lookup_follows_the_kernel_source(tmp_path, monkeypatch):
+    """bench.py's roofline.traffic comes from profiles/ncu_traffic.json and only while the profiled kernel's source file
+    still has the hash it was profiled with; a workload that was never profiled, another precision, or an edited source
+    gives None (never a stale literal)."""
+    import hashlib, json, os, sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    src = tmp_path / "csrc" / "k.cu"
+    src.parent.mkdir()
+    src.write_text("__global__ void k() {}\n")
+    (tmp_path / "profiles").mkdir()
+    ent = {"kernel": "k", "traffic_bytes": 1234, "dtype": "bf16", "source": "csrc/k.cu",
+           "source_sha16": hashlib.sha256(src.read_bytes()).hexdigest()[:16], "report": "profiles/x.txt"}
+    (tmp_path / "profiles" / "ncu_traffic.json").write_text(json.dumps({"wide4096": ent}))
+    monkeypatch.setattr(bench, "ROOT", str(tmp_path))
+    assert bench.profiled_traffic("wide4096", "bf16") == 1234
+    assert bench.profiled_traffic("wide4096", "fp32") is None
+    assert bench.profiled_traffic("wide8192", "bf16") is None
+    src.write_text("__global__ void k() { /* edited */ }\n")
+    assert bench.profiled_traffic("wide4096", "bf16") is None
+    # the committed table is current for the committed sources
+    monkeypatch.undo()
+    committed = json.load(open(os.path.join(bench.ROOT, "profiles", "ncu_traffic.json")))
+    for wl, e in committed.items():
+        assert bench.profiled_traffic(wl, "bf16") == e["traffic_bytes"], wl
