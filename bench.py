@@ -933,8 +933,12 @@ def run_reference(a):
         r = cpu_reference_run(wl, steps=a.steps, warmup=max(1, a.warmup))
     else:
         threads = max(1, cores // world)
-        env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE", "MASTER_ADDR",
-                                                                  "MASTER_PORT", "TORCHELASTIC_RUN_ID", "GROUP_RANK", "ROLE_RANK")}
+        # the workers rendezvous among themselves (tcp://127.0.0.1:port): nothing of the launcher's environment may reach
+        # them -- with TORCHELASTIC_USE_AGENT_STORE set, torch's tcp:// rendezvous turns every rank into a CLIENT of the
+        # elastic agent's store and waits for a server that does not exist on that port
+        drop = ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "GROUP_RANK", "ROLE_RANK",
+                "GROUP_WORLD_SIZE", "ROLE_WORLD_SIZE", "ROLE_NAME")
+        env = {k: v for k, v in os.environ.items() if k not in drop and not k.startswith("TORCHELASTIC_")}
         env["OMP_NUM_THREADS"] = str(threads)
         port = 29611 + (os.getpid() % 2000)
         procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--gpus", str(world),

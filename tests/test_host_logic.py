@@ -98,6 +98,25 @@ def test_bench_reference_arm_lines(tmp_path):
     assert r.returncode == 0 and r.stdout.strip() == ""
 
 
+def test_bench_reference_arm_under_torchrun():
+    """The driver launches `bench.py --impl reference --gpus N` under torchrun for N > 1.  The launcher's environment
+    (TORCHELASTIC_USE_AGENT_STORE above all: it turns a tcp:// rendezvous into a client of the agent's store) must not
+    reach the gloo workers rank 0 spawns -- the run once hung exactly there.  One line, rc 0, in bounded time."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT")}
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29541", os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "3",
+                        "--warmup", "1", "--workload", "tiny"], capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    line = json.loads(lines[0])
+    assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["value"] > 0 and "2 process(es)" in line["config"]["arm"]
+
+
 def test_bench_traffic_lookup_follows_the_kernel_source(tmp_path, monkeypatch):
     """bench.py's roofline.traffic comes from profiles/ncu_traffic.json and only while the profiled kernel's source file
     still has the hash it was profiled with; a workload that was never profiled, another precision, or an edited source
